@@ -1,0 +1,278 @@
+"""gputopo_b200 -- host-side mirror of the reference's scheduler-extender / device-plugin surface
+for the topology-aware GPU allocation path, over the C-ABI of libgputopo.so (include/gputopo.h).
+
+Python is the harness language here (the reference's Go toolchain is absent from this image); the
+product is the shared library.  Nothing in this package scores subsets on the CPU and nothing here
+imports oracle/: if the CUDA library is missing or no device is present, calls fail loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+INFEASIBLE = 0xFFFF0000
+NO_PLACE = 0xFFFFFFFFFFFFFFFF
+LV = dict(X=0, NVS=1, NV4=2, NV3=3, NV2=4, NV1=5, PSB=6, PIX=7, PXB=8, PHB=9, NODE=10, SYS=11)
+LUT_DEFAULT, LUT_DESIGN_MARKS = 0, 1
+K1_FIRST_UNUSED, K1_GAIA_SINGULAR = 0, 1
+
+EXPORTS = [
+    "gt_create", "gt_destroy", "gt_strerror", "gt_last_error", "gt_lut_preset", "gt_set_cost_lut",
+    "gt_score_int", "gt_score_milli", "gt_load_nodes", "gt_update_free", "gt_score_all", "gt_score_dirty",
+    "gt_best_node", "gt_allocate", "gt_commit", "gt_release", "gt_score_all_async", "gt_sync", "gt_stream",
+    "gt_device_best", "gt_num_nodes", "gt_launch_count", "gt_count_subsets", "gt_time_kernel",
+    "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster",
+]
+
+u8p = C.POINTER(C.c_uint8)
+u16p = C.POINTER(C.c_uint16)
+u32p = C.POINTER(C.c_uint32)
+u64p = C.POINTER(C.c_uint64)
+
+
+class GtConfig(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("max_nodes", C.c_uint32),
+                ("first_node", C.c_uint32), ("k1_policy", C.c_uint32), ("flags", C.c_uint32),
+                ("stream", C.c_void_p)]
+
+
+class GtError(RuntimeError):
+    def __init__(self, code, what, detail=""):
+        self.code = code
+        super().__init__("%s failed: %s (%d)%s" % (what, _lib().gt_strerror(code).decode(), code,
+                                                   (": " + detail) if detail else ""))
+
+
+_LIB = None
+
+
+def lib_path():
+    return os.path.join(HERE, "libgputopo.so")
+
+
+def _lib():
+    """Loads libgputopo.so (building it in-tree if the sources are newer).  No fallback."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    so = lib_path()
+    if _build.stale():
+        _build.build()
+    L = C.CDLL(so)
+    L.gt_strerror.restype = C.c_char_p
+    L.gt_last_error.restype = C.c_char_p
+    L.gt_last_error.argtypes = [C.c_void_p]
+    L.gt_create.argtypes = [C.POINTER(GtConfig), C.POINTER(C.c_void_p)]
+    L.gt_destroy.argtypes = [C.c_void_p]
+    L.gt_destroy.restype = None
+    L.gt_set_cost_lut.argtypes = [C.c_void_p, u8p]
+    L.gt_lut_preset.argtypes = [C.c_int, u8p]
+    for f in ("gt_score_int", "gt_score_milli"):
+        getattr(L, f).argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+    L.gt_load_nodes.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u8p, u8p, u16p, u16p]
+    L.gt_update_free.argtypes = [C.c_void_p, u32p, u16p, C.c_uint32]
+    L.gt_score_all.argtypes = [C.c_void_p, C.c_void_p]
+    L.gt_score_dirty.argtypes = [C.c_void_p]
+    L.gt_best_node.argtypes = [C.c_void_p, u8p, C.c_uint32, u64p]
+    L.gt_allocate.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u16p, u16p]
+    L.gt_commit.argtypes = [C.c_void_p, u32p, u16p, C.c_uint32]
+    L.gt_release.argtypes = [C.c_void_p, u32p, u16p, C.c_uint32]
+    L.gt_score_all_async.argtypes = [C.c_void_p]
+    L.gt_sync.argtypes = [C.c_void_p]
+    L.gt_stream.argtypes = [C.c_void_p]
+    L.gt_stream.restype = C.c_void_p
+    L.gt_device_best.argtypes = [C.c_void_p]
+    L.gt_device_best.restype = C.c_void_p
+    L.gt_num_nodes.argtypes = [C.c_void_p]
+    L.gt_num_nodes.restype = C.c_uint32
+    L.gt_launch_count.argtypes = [C.c_void_p]
+    L.gt_launch_count.restype = C.c_uint64
+    L.gt_count_subsets.argtypes = [C.c_void_p, u64p, u64p]
+    L.gt_time_kernel.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_float)]
+    L.gt_comm_unique_id.argtypes = [u8p]
+    L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
+    L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
+    _LIB = L
+    return L
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+def lut_preset(preset=LUT_DEFAULT):
+    out = np.zeros(16, np.uint8)
+    rc = _lib().gt_lut_preset(preset, _p(out, u8p))
+    if rc:
+        raise GtError(rc, "gt_lut_preset")
+    return out
+
+
+def score_int(s, length, cmax):
+    return int(_lib().gt_score_int(s, length, cmax))
+
+
+def score_milli(s, length, cmax):
+    return int(_lib().gt_score_milli(s, length, cmax))
+
+
+def synth_cluster(config, seed, first, count, gaia=False):
+    """Synthetic cluster of SURVEY.md section 8d: (levels[count,256], n_gpus, free, cls[, access, sibling])."""
+    lv = np.zeros((count, 256), np.uint8)
+    n = np.zeros(count, np.uint8)
+    fr = np.zeros(count, np.uint16)
+    cl = np.zeros(count, np.uint8)
+    ac = np.zeros((count, 16), np.uint8) if gaia else None
+    sib = np.zeros((count, 16), np.uint16) if gaia else None
+    rc = _lib().gt_synth_cluster(config, seed, first, count, _p(lv, u8p), _p(n, u8p), _p(fr, u16p), _p(cl, u8p),
+                                 _p(ac, u8p), _p(sib, u16p))
+    if rc:
+        raise GtError(rc, "gt_synth_cluster")
+    return (lv, n, fr, cl, ac, sib) if gaia else (lv, n, fr, cl)
+
+
+def comm_unique_id():
+    out = np.zeros(128, np.uint8)
+    rc = _lib().gt_comm_unique_id(_p(out, u8p))
+    if rc:
+        raise GtError(rc, "gt_comm_unique_id")
+    return out
+
+
+class Allocator:
+    """One context = one GPU's shard of the cluster (nodes [first_node, first_node + max_nodes))."""
+
+    def __init__(self, max_nodes, device=0, first_node=0, k1_policy=K1_FIRST_UNUSED, stream=None):
+        self._L = _lib()
+        cfg = GtConfig(C.sizeof(GtConfig), device, max_nodes, first_node, k1_policy, 0, stream)
+        h = C.c_void_p()
+        rc = self._L.gt_create(C.byref(cfg), C.byref(h))
+        if rc:
+            raise GtError(rc, "gt_create")
+        self._h = h
+        self.max_nodes = max_nodes
+        self.first_node = first_node
+
+    def _ck(self, rc, what):
+        if rc:
+            raise GtError(rc, what, self._L.gt_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.gt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def num_nodes(self):
+        return int(self._L.gt_num_nodes(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self._L.gt_launch_count(self._h))
+
+    @property
+    def stream(self):
+        return self._L.gt_stream(self._h)
+
+    @property
+    def device_best_ptr(self):
+        return self._L.gt_device_best(self._h)
+
+    def set_cost_lut(self, lut):
+        lut = np.ascontiguousarray(lut, np.uint8)
+        assert lut.size == 16
+        self._ck(self._L.gt_set_cost_lut(self._h, _p(lut, u8p)), "gt_set_cost_lut")
+
+    def load_nodes(self, levels, n_gpus, free, first=0, access_cost=None, sibling_mask=None):
+        levels = np.ascontiguousarray(levels, np.uint8).reshape(-1, 256)
+        n_gpus = np.ascontiguousarray(n_gpus, np.uint8)
+        free = np.ascontiguousarray(free, np.uint16)
+        count = len(n_gpus)
+        assert levels.shape[0] == count and free.shape[0] == count
+        ac = np.ascontiguousarray(access_cost, np.uint8) if access_cost is not None else None
+        sib = np.ascontiguousarray(sibling_mask, np.uint16) if sibling_mask is not None else None
+        self._ck(self._L.gt_load_nodes(self._h, first, count, _p(levels, u8p), _p(n_gpus, u8p), _p(ac, u8p),
+                                       _p(sib, u16p), _p(free, u16p)), "gt_load_nodes")
+
+    def update_free(self, masks, node_ids=None):
+        masks = np.ascontiguousarray(masks, np.uint16)
+        ids = np.ascontiguousarray(node_ids, np.uint32) if node_ids is not None else None
+        self._ck(self._L.gt_update_free(self._h, _p(ids, u32p), _p(masks, u16p), len(masks)), "gt_update_free")
+
+    def score_all(self, out=None, fetch=True):
+        """Prioritize for every node and every k.  Returns best[n_nodes,16] (u32 cost<<16|mask)."""
+        n = self.num_nodes
+        if fetch and out is None:
+            out = np.empty((n, 16), np.uint32)
+        ptr = out.ctypes.data if (fetch and out is not None) else None
+        self._ck(self._L.gt_score_all(self._h, ptr), "gt_score_all")
+        return out if fetch else None
+
+    def score_all_into(self, host_ptr):
+        self._ck(self._L.gt_score_all(self._h, host_ptr), "gt_score_all")
+
+    def score_dirty(self):
+        self._ck(self._L.gt_score_dirty(self._h), "gt_score_dirty")
+
+    def score_all_async(self):
+        self._ck(self._L.gt_score_all_async(self._h), "gt_score_all_async")
+
+    def sync(self):
+        self._ck(self._L.gt_sync(self._h), "gt_sync")
+
+    def best_node(self, ks):
+        ks = np.ascontiguousarray(ks, np.uint8)
+        out = np.zeros(len(ks), np.uint64)
+        self._ck(self._L.gt_best_node(self._h, _p(ks, u8p), len(ks), _p(out, u64p)), "gt_best_node")
+        return out
+
+    def allocate(self, node, k):
+        m = C.c_uint16(0)
+        c = C.c_uint16(0)
+        self._ck(self._L.gt_allocate(self._h, node, k, C.byref(m), C.byref(c)), "gt_allocate")
+        return int(m.value), int(c.value)
+
+    def commit(self, nodes, masks):
+        nodes = np.ascontiguousarray(nodes, np.uint32)
+        masks = np.ascontiguousarray(masks, np.uint16)
+        self._ck(self._L.gt_commit(self._h, _p(nodes, u32p), _p(masks, u16p), len(nodes)), "gt_commit")
+
+    def release(self, nodes, masks):
+        nodes = np.ascontiguousarray(nodes, np.uint32)
+        masks = np.ascontiguousarray(masks, np.uint16)
+        self._ck(self._L.gt_release(self._h, _p(nodes, u32p), _p(masks, u16p), len(nodes)), "gt_release")
+
+    def count_subsets(self):
+        s = C.c_uint64(0)
+        a = C.c_uint64(0)
+        self._ck(self._L.gt_count_subsets(self._h, C.byref(s), C.byref(a)), "gt_count_subsets")
+        return int(s.value), int(a.value)
+
+    def time_kernel(self, which, iters=20):
+        ms = C.c_float(0)
+        self._ck(self._L.gt_time_kernel(self._h, which.encode(), iters, C.byref(ms)), "gt_time_kernel")
+        return float(ms.value)
+
+    def comm_init(self, unique_id, rank, world):
+        uid = np.ascontiguousarray(unique_id, np.uint8)
+        self._ck(self._L.gt_comm_init(self._h, _p(uid, u8p), rank, world), "gt_comm_init")
+
+
+def place_fields(key):
+    key = int(key)
+    return key >> 48, (key >> 16) & 0xFFFFFFFF, key & 0xFFFF

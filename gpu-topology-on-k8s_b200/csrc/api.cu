@@ -1,0 +1,594 @@
+// api.cu -- the C-ABI of libgputopo.so (include/gputopo.h): context, tables in HBM, launches.
+// No CPU fallback lives here: scoring only ever happens in the kernels of kernels.cuh.
+#include "../../include/gputopo.h"
+#include "kernels.cuh"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct NcclId { char internal[128]; };
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(NcclId *) = nullptr;
+    int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclUint64 = 5;  // ncclUint64 in nccl.h
+constexpr int kNcclMin = 3;     // ncclMin
+
+NcclApi *nccl_api()
+{
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.handle ? &api : nullptr;
+    tried = true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+        api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+    }
+    if (!api.handle) return nullptr;
+    api.GetUniqueId = (int (*)(NcclId *))dlsym(api.handle, "ncclGetUniqueId");
+    api.CommInitRank = (int (*)(void **, int, NcclId, int))dlsym(api.handle, "ncclCommInitRank");
+    api.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(api.handle, "ncclAllReduce");
+    api.CommDestroy = (int (*)(void *))dlsym(api.handle, "ncclCommDestroy");
+    api.GetErrorString = (const char *(*)(int))dlsym(api.handle, "ncclGetErrorString");
+    if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy) {
+        api.handle = nullptr;
+        return nullptr;
+    }
+    return &api;
+}
+
+}  // namespace
+
+struct gt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint32_t cap = 0, n_nodes = 0, first_node = 0, k1_policy = 0;
+    int num_sms = 148;
+    uint8_t lut[16];
+    // HBM tables (SoA)
+    uint8_t *d_levels = nullptr, *d_cost = nullptr, *d_ngpus = nullptr;
+    uint8_t *d_access = nullptr;
+    uint16_t *d_sibling = nullptr;
+    uint16_t *d_free = nullptr;
+    uint32_t *d_best = nullptr;
+    uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1
+    unsigned long long *d_place = nullptr;
+    uint32_t *d_ids = nullptr;
+    uint16_t *d_masks = nullptr;
+    uint32_t *d_peak_out = nullptr;
+    // pinned host mirrors
+    uint16_t *h_free = nullptr;
+    uint8_t *h_ngpus = nullptr;
+    uint32_t *h_ids = nullptr;
+    uint16_t *h_masks = nullptr;
+    unsigned long long *h_place = nullptr;
+    uint32_t *h_row = nullptr;
+    std::vector<uint8_t> dirty_flag;
+    std::vector<uint32_t> dirty;
+    bool free_uploaded = true;    // device free[] equals the mirror except for `dirty`
+    bool best_valid = false, place_valid = false;
+    uint64_t launches = 0;
+    void *comm = nullptr;
+    int rank = 0, world = 1;
+    char err[256];
+};
+
+namespace {
+
+int fail(gt_ctx *c, int code, const char *fmt, const char *detail = "")
+{
+    if (c) snprintf(c->err, sizeof c->err, fmt, detail);
+    return code;
+}
+
+#define GT_CUDA(c, call)                                                          \
+    do {                                                                          \
+        cudaError_t e__ = (call);                                                 \
+        if (e__ != cudaSuccess) {                                                 \
+            if (c) snprintf((c)->err, sizeof(c)->err, "%s: %s", #call, cudaGetErrorString(e__)); \
+            return e__ == cudaErrorMemoryAllocation ? GT_ERR_NOMEM : GT_ERR_CUDA; \
+        }                                                                         \
+    } while (0)
+
+uint4 lut_as_uint4(const uint8_t lut[16])
+{
+    uint4 v;
+    memcpy(&v, lut, 16);
+    return v;
+}
+
+int apply_lut(gt_ctx *c, uint32_t first, uint32_t count)
+{
+    if (!count) return GT_OK;
+    const size_t n16 = (size_t)count * 16;   // 256 B per node = 16 uint4
+    const int grid = (int)std::min<size_t>((n16 + 255) / 256, (size_t)c->num_sms * 8);
+    gt::k_apply_lut<<<grid, 256, 0, c->stream>>>(c->d_levels + (size_t)first * 256, c->d_cost + (size_t)first * 256,
+                                                 n16, lut_as_uint4(c->lut));
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+__global__ void k_scatter_free(const uint32_t *ids, const uint16_t *masks, uint32_t n, uint16_t *free_mask)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) free_mask[ids[i]] = masks[i];
+}
+
+// bring the device free[] up to date with the host mirror
+int flush_free(gt_ctx *c, bool all)
+{
+    if (!c->n_nodes) return GT_OK;
+    if (all || !c->free_uploaded) {
+        GT_CUDA(c, cudaMemcpyAsync(c->d_free, c->h_free, (size_t)c->n_nodes * 2, cudaMemcpyHostToDevice, c->stream));
+        c->free_uploaded = true;
+        return GT_OK;
+    }
+    const uint32_t n = (uint32_t)c->dirty.size();
+    if (!n) return GT_OK;
+    for (uint32_t i = 0; i < n; i++) {
+        c->h_ids[i] = c->dirty[i];
+        c->h_masks[i] = c->h_free[c->dirty[i]];
+    }
+    GT_CUDA(c, cudaMemcpyAsync(c->d_ids, c->h_ids, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    GT_CUDA(c, cudaMemcpyAsync(c->d_masks, c->h_masks, (size_t)n * 2, cudaMemcpyHostToDevice, c->stream));
+    k_scatter_free<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_ids, c->d_masks, n, c->d_free);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+void clear_dirty(gt_ctx *c)
+{
+    for (uint32_t id : c->dirty) c->dirty_flag[id] = 0;
+    c->dirty.clear();
+}
+
+void mark_dirty(gt_ctx *c, uint32_t node)
+{
+    if (!c->dirty_flag[node]) {
+        c->dirty_flag[node] = 1;
+        c->dirty.push_back(node);
+    }
+    c->place_valid = false;
+}
+
+gt::ScoreParams score_params(gt_ctx *c)
+{
+    gt::ScoreParams p;
+    p.cost = c->d_cost; p.n_gpus = c->d_ngpus; p.free_mask = c->d_free; p.best = c->d_best;
+    p.bin_cnt = c->d_bin_cnt; p.bin_list = c->d_bin_list; p.cap = c->cap;
+    return p;
+}
+
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
+{
+    GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kBins * sizeof(uint32_t), c->stream));
+    gt::k_bin<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(c->d_ngpus, c->d_free, d_ids, n, c->cap,
+                                                                       c->d_bin_cnt, c->d_bin_list);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+int launch_score(gt_ctx *c, uint32_t n)
+{
+    const uint32_t grid = std::min<uint32_t>(n + gt::kBins, (uint32_t)c->num_sms * 8);
+    gt::k_score<<<grid, gt::kCta, 0, c->stream>>>(score_params(c));
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+int launch_argmin(gt_ctx *c)
+{
+    GT_CUDA(c, cudaMemsetAsync(c->d_place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
+    const size_t total = (size_t)c->n_nodes * 16;
+    const uint32_t grid = (uint32_t)std::min<size_t>((total + gt::kCta * 4 - 1) / (gt::kCta * 4), (size_t)c->num_sms * 4);
+    gt::k_argmin<<<std::max(grid, 1u), gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, c->first_node, c->d_place);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+// K0 + K1 over `n` nodes (all, or the listed ones), then K2 over the whole table
+int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
+{
+    int rc;
+    if (n) {
+        if ((rc = launch_bin(c, d_ids, n)) != GT_OK) return rc;
+        if ((rc = launch_score(c, n)) != GT_OK) return rc;
+    }
+    if ((rc = launch_argmin(c)) != GT_OK) return rc;
+    if (c->comm) {
+        NcclApi *api = nccl_api();
+        int e = api->AllReduce(c->d_place, c->d_place, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
+        if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    }
+    c->best_valid = true;
+    c->place_valid = true;
+    return GT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *gt_strerror(int status)
+{
+    switch (status) {
+    case GT_OK: return "ok";
+    case GT_ERR_INVALID: return "invalid argument";
+    case GT_ERR_NO_DEVICE: return "no usable CUDA device";
+    case GT_ERR_CUDA: return "CUDA error";
+    case GT_ERR_NOMEM: return "out of memory";
+    case GT_ERR_RANGE: return "node index out of range";
+    case GT_ERR_PARSE: return "parse error";
+    case GT_ERR_NCCL: return "NCCL error";
+    case GT_ERR_STATE: return "call out of order";
+    default: return "unknown status";
+    }
+}
+
+const char *gt_last_error(const gt_ctx *ctx) { return ctx ? ctx->err : ""; }
+
+int gt_create(const gt_config *cfg, gt_ctx **out)
+{
+    if (!cfg || !out || cfg->struct_size < sizeof(gt_config) || cfg->max_nodes == 0) return GT_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return GT_ERR_NO_DEVICE;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return GT_ERR_INVALID;
+    gt_ctx *c = new (std::nothrow) gt_ctx();
+    if (!c) return GT_ERR_NOMEM;
+    c->err[0] = 0;
+    c->device = cfg->device;
+    c->cap = cfg->max_nodes;
+    c->first_node = cfg->first_node;
+    c->k1_policy = cfg->k1_policy;
+    gt_lut_preset(GT_LUT_DEFAULT, c->lut);
+    int rc = [&]() -> int {
+        GT_CUDA(c, cudaSetDevice(c->device));
+        cudaDeviceProp prop;
+        GT_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
+        c->num_sms = prop.multiProcessorCount;
+        if (cfg->stream) {
+            c->stream = (cudaStream_t)cfg->stream;
+        } else {
+            GT_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+            c->own_stream = true;
+        }
+        const size_t N = c->cap;
+        GT_CUDA(c, cudaMalloc(&c->d_levels, N * 256));
+        GT_CUDA(c, cudaMalloc(&c->d_cost, N * 256));
+        GT_CUDA(c, cudaMalloc(&c->d_ngpus, N));
+        GT_CUDA(c, cudaMalloc(&c->d_access, N * 16));
+        GT_CUDA(c, cudaMalloc(&c->d_sibling, N * 32));
+        GT_CUDA(c, cudaMalloc(&c->d_free, N * 2));
+        GT_CUDA(c, cudaMalloc(&c->d_best, N * 64));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, gt::kBins * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_place, 16 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
+        GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
+        GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
+        GT_CUDA(c, cudaMemset(c->d_ngpus, 0, N));
+        GT_CUDA(c, cudaMemset(c->d_free, 0, N * 2));
+        GT_CUDA(c, cudaMemset(c->d_levels, 0, N * 256));
+        GT_CUDA(c, cudaMemset(c->d_cost, 0, N * 256));
+        GT_CUDA(c, cudaMemset(c->d_access, 0, N * 16));
+        GT_CUDA(c, cudaMemset(c->d_sibling, 0, N * 32));
+        GT_CUDA(c, cudaHostAlloc(&c->h_free, N * 2, cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_ngpus, N, cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_ids, N * 4, cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_masks, N * 2, cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_place, 16 * sizeof(unsigned long long), cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_row, 64, cudaHostAllocDefault));
+        memset(c->h_free, 0, N * 2);
+        memset(c->h_ngpus, 0, N);
+        c->dirty_flag.assign(N, 0);
+        return GT_OK;
+    }();
+    if (rc != GT_OK) {
+        fprintf(stderr, "gt_create: %s\n", c->err);
+        gt_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return GT_OK;
+}
+
+void gt_destroy(gt_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm) {
+        NcclApi *api = nccl_api();
+        if (api) api->CommDestroy(c->comm);
+    }
+    cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
+    cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_place);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out);
+    cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
+    cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int gt_set_cost_lut(gt_ctx *c, const uint8_t lut[16])
+{
+    if (!c || !lut) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    memcpy(c->lut, lut, 16);
+    c->best_valid = c->place_valid = false;
+    int rc = apply_lut(c, 0, c->n_nodes);
+    if (rc != GT_OK) return rc;
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GT_OK;
+}
+
+int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *levels, const uint8_t *n_gpus,
+                  const uint8_t *access_cost, const uint16_t *sibling_mask, const uint16_t *free_mask)
+{
+    if (!c || !levels || !n_gpus || !free_mask) return GT_ERR_INVALID;
+    if ((uint64_t)first + count > c->cap) return fail(c, GT_ERR_RANGE, "gt_load_nodes: first+count exceeds max_nodes%s");
+    if (!count) return GT_OK;
+    for (uint32_t i = 0; i < count; i++)
+        if (n_gpus[i] > GT_MAX_GPUS) return fail(c, GT_ERR_INVALID, "gt_load_nodes: n_gpus > 16%s");
+    GT_CUDA(c, cudaSetDevice(c->device));
+    GT_CUDA(c, cudaMemcpyAsync(c->d_levels + (size_t)first * 256, levels, (size_t)count * 256, cudaMemcpyHostToDevice, c->stream));
+    memcpy(c->h_ngpus + first, n_gpus, count);
+    memcpy(c->h_free + first, free_mask, (size_t)count * 2);
+    GT_CUDA(c, cudaMemcpyAsync(c->d_ngpus + first, c->h_ngpus + first, count, cudaMemcpyHostToDevice, c->stream));
+    GT_CUDA(c, cudaMemcpyAsync(c->d_free + first, c->h_free + first, (size_t)count * 2, cudaMemcpyHostToDevice, c->stream));
+    if (access_cost)
+        GT_CUDA(c, cudaMemcpyAsync(c->d_access + (size_t)first * 16, access_cost, (size_t)count * 16, cudaMemcpyHostToDevice, c->stream));
+    if (sibling_mask)
+        GT_CUDA(c, cudaMemcpyAsync(c->d_sibling + (size_t)first * 16, sibling_mask, (size_t)count * 32, cudaMemcpyHostToDevice, c->stream));
+    c->n_nodes = std::max(c->n_nodes, first + count);
+    int rc = apply_lut(c, first, count);
+    if (rc != GT_OK) return rc;
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));   // caller buffers are free to change after return
+    c->best_valid = c->place_valid = false;
+    return GT_OK;
+}
+
+int gt_update_free(gt_ctx *c, const uint32_t *node_ids, const uint16_t *masks, uint32_t count)
+{
+    if (!c || !masks) return GT_ERR_INVALID;
+    if (!node_ids) {
+        if (count > c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_update_free: count exceeds loaded nodes%s");
+        memcpy(c->h_free, masks, (size_t)count * 2);
+        if (count == c->n_nodes) {       // whole shard: one bulk copy, every node rescored by the next gt_score_all
+            c->free_uploaded = false;
+            clear_dirty(c);
+            c->best_valid = c->place_valid = false;
+            return GT_OK;
+        }
+        for (uint32_t i = 0; i < count; i++) mark_dirty(c, i);
+        return GT_OK;
+    }
+    for (uint32_t i = 0; i < count; i++)
+        if (node_ids[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_update_free: node id out of range%s");
+    for (uint32_t i = 0; i < count; i++) {
+        c->h_free[node_ids[i]] = masks[i];
+        mark_dirty(c, node_ids[i]);
+    }
+    return GT_OK;
+}
+
+int gt_commit(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t count)
+{
+    if (!c || !nodes || !masks) return GT_ERR_INVALID;
+    for (uint32_t i = 0; i < count; i++) {
+        if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_commit: node id out of range%s");
+        if ((c->h_free[nodes[i]] & masks[i]) != masks[i]) return fail(c, GT_ERR_STATE, "gt_commit: GPU already in use%s");
+    }
+    for (uint32_t i = 0; i < count; i++) {
+        c->h_free[nodes[i]] &= (uint16_t)~masks[i];
+        mark_dirty(c, nodes[i]);
+    }
+    return GT_OK;
+}
+
+int gt_release(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t count)
+{
+    if (!c || !nodes || !masks) return GT_ERR_INVALID;
+    for (uint32_t i = 0; i < count; i++)
+        if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_release: node id out of range%s");
+    for (uint32_t i = 0; i < count; i++) {
+        c->h_free[nodes[i]] |= masks[i];
+        mark_dirty(c, nodes[i]);
+    }
+    return GT_OK;
+}
+
+int gt_score_all_async(gt_ctx *c)
+{
+    if (!c) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
+    if (rc != GT_OK) return rc;
+    clear_dirty(c);
+    return enqueue_scoring(c, nullptr, c->n_nodes);
+}
+
+int gt_sync(gt_ctx *c)
+{
+    if (!c) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GT_OK;
+}
+
+int gt_score_all(gt_ctx *c, uint32_t *out_best)
+{
+    int rc = gt_score_all_async(c);
+    if (rc != GT_OK) return rc;
+    if (out_best && c->n_nodes)
+        GT_CUDA(c, cudaMemcpyAsync(out_best, c->d_best, (size_t)c->n_nodes * 64, cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GT_OK;
+}
+
+int gt_score_dirty(gt_ctx *c)
+{
+    if (!c) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    if (!c->best_valid || !c->free_uploaded) return gt_score_all(c, nullptr);
+    const uint32_t n = (uint32_t)c->dirty.size();
+    int rc = flush_free(c, false);           // fills d_ids with the dirty list
+    if (rc != GT_OK) return rc;
+    clear_dirty(c);
+    rc = enqueue_scoring(c, c->d_ids, n);
+    if (rc != GT_OK) return rc;
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GT_OK;
+}
+
+int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place)
+{
+    if (!c || (nreq && (!k || !out_place))) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    if (!c->best_valid) return fail(c, GT_ERR_STATE, "gt_best_node: score first%s");
+    if (!c->dirty.empty() || !c->free_uploaded) return fail(c, GT_ERR_STATE, "gt_best_node: free masks changed, rescore first%s");
+    if (!c->place_valid) {
+        int rc = enqueue_scoring(c, nullptr, 0);
+        if (rc != GT_OK) return rc;
+    }
+    GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->d_place, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < nreq; i++)
+        out_place[i] = (k[i] >= 1 && k[i] <= 16) ? (uint64_t)c->h_place[k[i] - 1] : GT_NO_PLACE;
+    return GT_OK;
+}
+
+int gt_allocate(gt_ctx *c, uint32_t node, uint32_t k, uint16_t *out_mask, uint16_t *out_cost)
+{
+    if (!c || !out_mask || !out_cost || k < 1 || k > 16) return GT_ERR_INVALID;
+    if (node >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_allocate: node id out of range%s");
+    if (!c->best_valid) return fail(c, GT_ERR_STATE, "gt_allocate: score first%s");
+    if (c->dirty_flag[node] || !c->free_uploaded) return fail(c, GT_ERR_STATE, "gt_allocate: node changed, rescore first%s");
+    GT_CUDA(c, cudaSetDevice(c->device));
+    GT_CUDA(c, cudaMemcpyAsync(c->h_row, c->d_best + (size_t)node * 16, 64, cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    *out_mask = (uint16_t)GT_BEST_MASK(c->h_row[k - 1]);
+    *out_cost = (uint16_t)GT_BEST_COST(c->h_row[k - 1]);
+    return GT_OK;
+}
+
+void *gt_stream(gt_ctx *c) { return c ? (void *)c->stream : nullptr; }
+const uint32_t *gt_device_best(gt_ctx *c) { return c ? c->d_best : nullptr; }
+uint32_t gt_num_nodes(const gt_ctx *c) { return c ? c->n_nodes : 0; }
+uint64_t gt_launch_count(const gt_ctx *c) { return c ? c->launches : 0; }
+
+int gt_count_subsets(gt_ctx *c, uint64_t *out_subsets, uint64_t *out_pair_adds)
+{
+    if (!c) return GT_ERR_INVALID;
+    uint64_t s = 0, a = 0;
+    for (uint32_t i = 0; i < c->n_nodes; i++) {
+        const uint32_t ng = c->h_ngpus[i];
+        const uint32_t f = c->h_free[i] & ((1u << ng) - 1u);
+        const uint32_t p = (uint32_t)__builtin_popcount(f);
+        s += (1ull << p) - 1;
+        if (p >= 2) a += (uint64_t)(p * (p - 1) / 2) << (p - 2);
+    }
+    if (out_subsets) *out_subsets = s;
+    if (out_pair_adds) *out_pair_adds = a;
+    return GT_OK;
+}
+
+int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
+{
+    if (!c || !which || !out_ms || !iters) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
+    if (rc != GT_OK) return rc;
+    clear_dirty(c);
+    cudaEvent_t e0, e1;
+    GT_CUDA(c, cudaEventCreate(&e0));
+    GT_CUDA(c, cudaEventCreate(&e1));
+    const std::string w(which);
+    const uint32_t peak_iters = 2048;
+    auto one = [&]() -> int {
+        if (w == "bin") return launch_bin(c, nullptr, c->n_nodes);
+        if (w == "score") return launch_score(c, c->n_nodes);
+        if (w == "argmin") return launch_argmin(c);
+        if (w == "int32_peak") {
+            gt::k_int32_peak<<<c->num_sms * 8, gt::kCta, 0, c->stream>>>(c->d_peak_out, peak_iters, 12345u);
+            c->launches++;
+            return GT_OK;
+        }
+        return GT_ERR_INVALID;
+    };
+    if (w == "score" || w == "argmin") {   // bins / best table must exist
+        if ((rc = launch_bin(c, nullptr, c->n_nodes)) != GT_OK) return rc;
+        if ((rc = launch_score(c, c->n_nodes)) != GT_OK) return rc;
+    }
+    if ((rc = one()) != GT_OK) return rc;   // warm-up
+    GT_CUDA(c, cudaEventRecord(e0, c->stream));
+    for (uint32_t i = 0; i < iters; i++)
+        if ((rc = one()) != GT_OK) return rc;
+    GT_CUDA(c, cudaEventRecord(e1, c->stream));
+    GT_CUDA(c, cudaEventSynchronize(e1));
+    float ms = 0;
+    GT_CUDA(c, cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (w == "bin") {   // leave the pipeline consistent
+        if ((rc = launch_score(c, c->n_nodes)) != GT_OK) return rc;
+        GT_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->best_valid = true;
+    }
+    *out_ms = ms / (float)iters;
+    return GT_OK;
+}
+
+int gt_comm_unique_id(uint8_t out_id[128])
+{
+    NcclApi *api = nccl_api();
+    if (!api || !out_id) return GT_ERR_NCCL;
+    NcclId id;
+    if (api->GetUniqueId(&id) != 0) return GT_ERR_NCCL;
+    memcpy(out_id, id.internal, 128);
+    return GT_OK;
+}
+
+int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
+{
+    if (!c || !id || world < 1 || rank < 0 || rank >= world) return GT_ERR_INVALID;
+    NcclApi *api = nccl_api();
+    if (!api) return fail(c, GT_ERR_NCCL, "libnccl.so.2 not loadable%s");
+    GT_CUDA(c, cudaSetDevice(c->device));
+    NcclId nid;
+    memcpy(nid.internal, id, 128);
+    int e = api->CommInitRank(&c->comm, world, nid, rank);
+    if (e != 0) {
+        c->comm = nullptr;
+        return fail(c, GT_ERR_NCCL, "ncclCommInitRank: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    }
+    c->rank = rank;
+    c->world = world;
+    c->place_valid = false;
+    return GT_OK;
+}
+
+}  // extern "C"

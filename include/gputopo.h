@@ -1,0 +1,143 @@
+/*
+ * gputopo.h -- C-ABI of libgputopo.so: the topology-aware GPU allocation hot path of
+ * hellolijj/gpu-topology-on-k8s (design.md section 2.2 "scheduler extender scoring") on B200.
+ *
+ * The reference is a design document with Go snippets and no allocator source; "replaces" below
+ * cites the place in the reference documents that specifies the behaviour each entry point
+ * implements (design.md:N = /root/reference/design.md line N; Alg. n = Gaia paper algorithms in
+ * /root/reference/reference/gaia_gpu_topology/).  A Go extender binds these through cgo
+ * (INTEGRATION.md).
+ *
+ * Conventions: every buffer is caller-owned; inputs are copied before the call returns and no
+ * caller pointer is retained (cgo pointer rules).  All functions return 0 on success or a negative
+ * gt_status; nothing throws or aborts across this boundary.  "Fewer than k free GPUs" is not an
+ * error: the entry is GT_INFEASIBLE (mask 0, cost 0xFFFF).  A context is used by one caller at a
+ * time (not thread-safe), matching kube-scheduler's one-pod-at-a-time loop.  There is no CPU
+ * fallback: without a CUDA device gt_create fails with GT_ERR_NO_DEVICE.
+ */
+#ifndef GPUTOPO_H
+#define GPUTOPO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GT_MAX_GPUS 16
+#define GT_INFEASIBLE 0xFFFF0000u
+
+/* best[node][k-1] entry: cost<<16 | gpu mask */
+#define GT_BEST_COST(b) ((uint32_t)(b) >> 16)
+#define GT_BEST_MASK(b) ((uint32_t)(b) & 0xFFFFu)
+/* placement key: cost<<48 | global node index<<16 | gpu mask; GT_NO_PLACE when no node can host the request */
+#define GT_NO_PLACE 0xFFFFFFFFFFFFFFFFull
+#define GT_PLACE_COST(p) ((uint32_t)((uint64_t)(p) >> 48))
+#define GT_PLACE_NODE(p) ((uint32_t)(((uint64_t)(p) >> 16) & 0xFFFFFFFFu))
+#define GT_PLACE_MASK(p) ((uint32_t)((uint64_t)(p) & 0xFFFFu))
+
+typedef enum gt_status {
+    GT_OK = 0,
+    GT_ERR_INVALID = -1,     /* bad argument */
+    GT_ERR_NO_DEVICE = -2,   /* no usable CUDA device / driver */
+    GT_ERR_CUDA = -3,        /* a CUDA call failed; see gt_last_error */
+    GT_ERR_NOMEM = -4,
+    GT_ERR_RANGE = -5,       /* node index / count beyond the context's capacity */
+    GT_ERR_PARSE = -6,       /* malformed topology text / annotation */
+    GT_ERR_NCCL = -7,
+    GT_ERR_STATE = -8        /* call order (e.g. allocate before score) */
+} gt_status;
+
+/* Link-level codes.  replaces: the P2PLinkType table design.md:33-44 (+ NVSwitch, absent there). Lower = closer. */
+enum {
+    GT_LV_X = 0, GT_LV_NVS = 1, GT_LV_NV4 = 2, GT_LV_NV3 = 3, GT_LV_NV2 = 4, GT_LV_NV1 = 5,
+    GT_LV_PSB = 6, GT_LV_PIX = 7, GT_LV_PXB = 8, GT_LV_PHB = 9, GT_LV_NODE = 10, GT_LV_SYS = 11
+};
+enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
+enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
+
+typedef struct gt_ctx gt_ctx;
+
+typedef struct gt_config {
+    uint32_t struct_size;  /* sizeof(gt_config) */
+    int32_t device;        /* CUDA device ordinal */
+    uint32_t max_nodes;    /* capacity of this context (its shard of the cluster) */
+    uint32_t first_node;   /* global index of local node 0: placement keys carry first_node + local */
+    uint32_t k1_policy;    /* GT_K1_*: design.md:154-160 first unused device, or Gaia Alg. 3 */
+    uint32_t flags;        /* reserved, 0 */
+    void *stream;          /* optional cudaStream_t to launch on; NULL = the library creates one */
+} gt_config;
+
+/* ---- life cycle ---- */
+int gt_create(const gt_config *cfg, gt_ctx **out);
+void gt_destroy(gt_ctx *ctx);
+const char *gt_strerror(int status);
+const char *gt_last_error(const gt_ctx *ctx);
+
+/* ---- link table / score (host only) ---- */
+/* replaces: bandwidth-weight column design.md:33-47 (left "TODO") and mark table design.md:196-203 */
+int gt_lut_preset(int preset, uint8_t out_lut[16]);
+int gt_set_cost_lut(gt_ctx *ctx, const uint8_t lut[16]);
+/* replaces: score formula design.md:205-217.  floor(10*(cmax*len-sum)/(cmax*len)), len = C(k,2) */
+int gt_score_int(uint32_t sum, uint32_t len, uint32_t cmax);
+int gt_score_milli(uint32_t sum, uint32_t len, uint32_t cmax);
+
+/* ---- topology tables ---- */
+/* replaces: type gpuTopology map[uint]map[uint]gpuTopologyType design.md:64-70 filled from the node
+ * annotations design.md:78-82; free = complement of the GPUs in ALIYUN_COM_GPU_GROUP of the pods on
+ * the node (design.md:231).  levels: count x 256 bytes (16x16 row-major GT_LV_* codes, entry [i][j]
+ * with i<j is the one read); n_gpus: count bytes; access_cost (count x 16) and sibling_mask
+ * (count x 16 u16) are optional (NULL) and only used by GT_K1_GAIA_SINGULAR; free_mask: count u16. */
+int gt_load_nodes(gt_ctx *ctx, uint32_t first, uint32_t count, const uint8_t *levels, const uint8_t *n_gpus,
+                  const uint8_t *access_cost, const uint16_t *sibling_mask, const uint16_t *free_mask);
+/* node_ids == NULL: masks are for nodes [0, count) */
+int gt_update_free(gt_ctx *ctx, const uint32_t *node_ids, const uint16_t *masks, uint32_t count);
+
+/* ---- the hot path ---- */
+/* replaces: PrioritizeVerb "sort" design.md:99,118 -- for every node the best GPU combination for
+ * every request size k = 1..16 (every k-subset of the free set, pair-cost sum design.md:208, lowest
+ * wins design.md:169, ties -> numerically lowest mask).  out_best: n_nodes x 16 u32 or NULL to leave
+ * the table on the device. */
+int gt_score_all(gt_ctx *ctx, uint32_t *out_best);
+/* same, for the nodes touched by gt_update_free / gt_commit / gt_release since the last scoring */
+int gt_score_dirty(gt_ctx *ctx);
+/* replaces: kube-scheduler's host choice after "sort" (design.md:115-119): for each request size
+ * k[i] the placement key of the best node (lowest cost, then lowest node index); with a
+ * communicator attached the minimum over all ranks. */
+int gt_best_node(gt_ctx *ctx, const uint8_t *k, uint32_t nreq, uint64_t *out_place);
+/* replaces: bindVerb "bind" GPU choice design.md:119 and what the device plugin's Allocate hands
+ * out design.md:239 -- the best combination of k GPUs on one node (local index). */
+int gt_allocate(gt_ctx *ctx, uint32_t node, uint32_t k, uint16_t *out_mask, uint16_t *out_cost);
+/* replaces: the state update of bind design.md:223-234 (pod recorded on the device) / pod deletion.
+ * Host commit loop: clears (commit) or sets (release) the bits and marks the node dirty. */
+int gt_commit(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32_t count);
+int gt_release(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32_t count);
+
+/* ---- asynchronous / measurement surface ---- */
+int gt_score_all_async(gt_ctx *ctx);     /* enqueue scoring + cluster argmin, no copies, no sync */
+int gt_sync(gt_ctx *ctx);
+void *gt_stream(gt_ctx *ctx);            /* the cudaStream_t work is enqueued on */
+const uint32_t *gt_device_best(gt_ctx *ctx);   /* device pointer of best[n_nodes][16] */
+uint32_t gt_num_nodes(const gt_ctx *ctx);
+uint64_t gt_launch_count(const gt_ctx *ctx);   /* kernels this context has launched */
+/* candidate subsets one full scoring pass covers: sum over nodes of 2^popcount(free)-1; optionally
+ * the algorithmic pair-cost additions sum C(f,2)*2^(f-2) */
+int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds);
+/* time `iters` back-to-back launches of one kernel ("bin", "score", "argmin", "int32_peak") with
+ * CUDA events on the context's stream; out_ms = average per launch */
+int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
+
+/* ---- multi-GPU: nodes are sharded, one context per GPU; the only exchange is a min over 16 keys ---- */
+int gt_comm_unique_id(uint8_t out_id[128]);
+int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
+
+/* ---- synthetic clusters for tests and benchmarks (splitmix64) ---- */
+int gt_synth_cluster(int config, uint64_t seed, uint32_t first, uint32_t count, uint8_t *levels,
+                     uint8_t *n_gpus, uint16_t *free_mask, uint8_t *class_out, uint8_t *access_cost,
+                     uint16_t *sibling_mask);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

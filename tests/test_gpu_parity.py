@@ -1,0 +1,185 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle: bit-exact, integer work.
+Run on the B200 box with `-m gpu`."""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+
+
+def all_masks_cluster(oracle, cls):
+    lv, n, _, _ = oracle.class_topology(cls)
+    N = 1 << n
+    levels = np.tile(lv, (N, 1))
+    n_gpus = np.full(N, n, np.uint8)
+    free = np.arange(N, dtype=np.uint16)
+    return levels, n_gpus, free
+
+
+def check_cluster(gt, oracle, levels, n_gpus, free, lut=None, threads=8):
+    lut = oracle.lut(0) if lut is None else lut
+    with gt.Allocator(len(n_gpus)) as a:
+        a.set_cost_lut(lut)
+        a.load_nodes(levels, n_gpus, free)
+        got = a.score_all()
+        want, cnt = oracle.exhaustive_cluster(levels, n_gpus, free, lut, threads)
+        assert a.count_subsets()[0] == cnt
+        bad = np.nonzero((got != want).any(axis=1))[0]
+        assert len(bad) == 0, "first mismatch node %d free=%#x got=%s want=%s" % (
+            bad[0], free[bad[0]], got[bad[0]], want[bad[0]])
+        place = a.best_node(np.arange(1, 17, dtype=np.uint8))
+        assert (place == oracle.cluster_argmin(want)).all()
+    return got
+
+
+@pytest.mark.parametrize("cls", ["DGX1", "F1_RING", "F2_PCIE", "F3_TREE4"])
+def test_every_free_mask_small_topologies(gt, oracle, cls):
+    """all 2^n free masks x all k for each fixture topology (3^8 = 6561 subsets)."""
+    check_cluster(gt, oracle, *all_masks_cluster(oracle, ol.CLS[cls]))
+
+
+@pytest.mark.parametrize("cls", ["NVS16", "DUAL8"])
+def test_every_free_mask_16_gpu_topologies(gt, oracle, cls):
+    """3^16 = 43 M subsets per topology, every free mask of a 16-GPU node."""
+    check_cluster(gt, oracle, *all_masks_cluster(oracle, ol.CLS[cls]))
+
+
+def test_random_matrices_and_luts(gt, oracle):
+    """Arbitrary (even asymmetric) level matrices and random u8 cost tables, n from 1 to 16."""
+    rng = np.random.RandomState(11)
+    N = 6000
+    levels = rng.randint(0, 16, (N, 256)).astype(np.uint8)
+    n_gpus = rng.randint(0, 17, N).astype(np.uint8)
+    free = rng.randint(0, 1 << 16, N).astype(np.uint16)
+    n_gpus[:200] = 16
+    free[:200] |= 0xFF00       # plenty of large free sets
+    free[200:232] = 0xFFFF
+    n_gpus[200:232] = 16
+    lut = rng.randint(0, 256, 16).astype(np.uint8)
+    check_cluster(gt, oracle, levels, n_gpus, free, lut)
+
+
+def test_known_answers_through_the_abi(gt, oracle):
+    """KA2, KA4b, KA6 (m >= 2) and the k = 1 'first unused device' convention, on the GPU."""
+    rows = [("F2_PCIE", [], 2, 0b11), ("F3_TREE4", [], 2, 0b1100), ("F3_TREE4", [2], 2, 0b0011)]
+    for cls, used, m, want in rows:
+        lv, n, _, _ = oracle.class_topology(ol.CLS[cls])
+        free = ((1 << n) - 1) & ~sum(1 << u for u in used)
+        with gt.Allocator(4) as a:
+            a.load_nodes(lv[None, :], [n], [free])
+            a.score_all()
+            mask, cost = a.allocate(0, m)
+            assert mask == want
+            assert a.allocate(0, 1)[0] == (free & -free)
+
+
+@pytest.mark.parametrize("config,seed,N", [(2, 0x5EED0002, 1000), (3, 0x5EED0003, 3000), (33, 0x5EED0003, 3000),
+                                          (4, 0x5EED0004, 20000)])
+def test_synthetic_configs(gt, oracle, config, seed, N):
+    lv, n, fr, _ = gt.synth_cluster(config, seed, 0, N)
+    check_cluster(gt, oracle, lv, n, fr)
+
+
+def test_edge_cases(gt, oracle):
+    lv, n, _, _ = oracle.class_topology(ol.CLS["DGX1"])
+    lut = oracle.lut(0)
+    with gt.Allocator(8) as a:
+        # a single node; an empty node; n_gpus = 0; free bits above n_gpus
+        levels = np.tile(lv, (4, 1))
+        a.load_nodes(levels, [8, 8, 0, 8], [0xFF, 0x00, 0xFFFF, 0xFF0F])
+        got = a.score_all()
+        want, _ = oracle.exhaustive_cluster(levels, np.array([8, 8, 0, 8], np.uint8),
+                                            np.array([0xFF, 0, 0xFFFF, 0xFF0F], np.uint16), lut, 1)
+        assert (got == want).all()
+        assert (got[1] == ol.INFEASIBLE).all() and (got[2] == ol.INFEASIBLE).all()
+        place = a.best_node([1, 8, 9])
+        assert gt.place_fields(place[0]) == (0, 0, 1)
+        assert gt.place_fields(place[1])[1:] == (0, 0xFF)
+        assert int(place[2]) == gt.NO_PLACE
+        with pytest.raises(gt.GtError):
+            a.load_nodes(levels, [8, 8, 17, 8], [0, 0, 0, 0])
+        with pytest.raises(gt.GtError):
+            a.load_nodes(np.tile(lv, (9, 1)), [8] * 9, [0] * 9)
+
+
+def test_idempotent_and_lut_change(gt, oracle):
+    lv, n, fr, _ = gt.synth_cluster(4, 99, 0, 5000)
+    with gt.Allocator(5000) as a:
+        a.load_nodes(lv, n, fr)
+        b1 = a.score_all()
+        b2 = a.score_all()
+        assert (b1 == b2).all()
+        marks = oracle.lut(1)
+        a.set_cost_lut(marks)
+        b3 = a.score_all()
+        want, _ = oracle.exhaustive_cluster(lv, n, fr, marks, 8)
+        assert (b3 == want).all()
+
+
+def test_commit_release_rescore_dirty(gt, oracle):
+    """Host commit loop: commit / release mark nodes dirty, gt_score_dirty re-scores exactly those."""
+    lut = oracle.lut(0)
+    lv, n, fr, _ = gt.synth_cluster(2, 0x5EED0002, 0, 300)
+    free = fr.copy()
+    rng = np.random.RandomState(5)
+    with gt.Allocator(300) as a:
+        a.load_nodes(lv, n, free)
+        a.score_all(fetch=False)
+        live = []
+        for step in range(60):
+            ks = rng.randint(1, 9, 4).astype(np.uint8)
+            for k in ks:
+                place = a.best_node([k])[0]
+                want_best, _ = oracle.exhaustive_cluster(lv, n, free, lut, 4)
+                assert int(place) == int(oracle.cluster_argmin(want_best)[k - 1])
+                if int(place) == gt.NO_PLACE:
+                    continue
+                cost, node, mask = gt.place_fields(place)
+                assert a.allocate(node, int(k)) == (mask, cost)
+                a.commit([node], [mask])
+                free[node] &= ~mask & 0xFFFF
+                live.append((node, mask))
+                a.score_dirty()
+            if live and step % 3 == 0:
+                node, mask = live.pop(rng.randint(len(live)))
+                a.release([node], [mask])
+                free[node] |= mask
+                a.score_dirty()
+        got = a.score_all()
+        want, _ = oracle.exhaustive_cluster(lv, n, free, lut, 4)
+        assert (got == want).all()
+        with pytest.raises(gt.GtError):
+            a.commit([0], [0xFFFF])     # GPUs not free
+
+
+def test_full_size_properties(gt, oracle):
+    """BASELINE config 4 at its full 100 000 nodes: size-independent properties + a sampled oracle check."""
+    N = 100000
+    lv, n, fr, cl = gt.synth_cluster(4, 0x5EED0004, 0, N)
+    with gt.Allocator(N) as a:
+        a.load_nodes(lv, n, fr)
+        best = a.score_all()
+        mask = best & 0xFFFF
+        cost = best >> 16
+        pc = np.array([bin(int(x)).count("1") for x in (fr & ((1 << n.astype(np.uint32)) - 1))])
+        k = np.arange(1, 17)[None, :]
+        feas = k <= pc[:, None]
+        assert ((best == ol.INFEASIBLE) == ~feas).all()
+        # chosen GPUs are free, and exactly k of them
+        assert ((mask & ~fr[:, None].astype(np.uint32))[feas] == 0).all()
+        popc = np.zeros_like(mask)
+        for b in range(16):
+            popc += (mask >> b) & 1
+        assert (popc[feas] == np.broadcast_to(k, best.shape)[feas]).all()
+        # k = 1 costs nothing and takes the lowest free GPU; k = popcount takes everything
+        has1 = pc >= 1
+        assert (cost[has1, 0] == 0).all()
+        lowest = (fr & (~fr + 1)).astype(np.uint32)
+        assert (mask[has1, 0] == lowest[has1]).all()
+        # sampled rows against the oracle
+        idx = np.random.RandomState(1).choice(N, 4000, replace=False)
+        want, _ = oracle.exhaustive_cluster(lv[idx], n[idx], fr[idx], oracle.lut(0), 8)
+        assert (best[idx] == want).all()
+        # the cluster argmin is a checksum over the whole table
+        assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(best)).all()

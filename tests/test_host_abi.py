@@ -1,0 +1,71 @@
+"""CPU-side checks: the C-ABI library loads, exports every symbol include/gputopo.h declares, and its
+host-only pieces (LUT presets, score formula, synthetic clusters) agree with the oracle.  No GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "gputopo.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(gt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(gt):
+    L = C.CDLL(gt.lib_path())
+    syms = declared_symbols()
+    assert len(syms) >= 25
+    for s in syms:
+        assert hasattr(L, s), "libgputopo.so does not export %s" % s
+    # and the python mirror binds all of them
+    assert set(gt.EXPORTS) == set(syms)
+
+
+def test_no_device_fails_loudly(gt):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(gt.GtError) as e:
+        gt.Allocator(16)
+    assert e.value.code == -2
+
+
+def test_product_does_not_reference_oracle():
+    pkg = os.path.join(ROOT, "gpu-topology-on-k8s_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert "oracle" not in src.replace("no CPU fallback", "").lower() or f == "__init__.py" and \
+                    "imports oracle/" in src, f
+    assert "oracle" not in open(os.path.join(ROOT, "include", "gputopo.h")).read().lower()
+
+
+def test_lut_presets_and_score_match_oracle(gt, oracle):
+    for preset in (0, 1):
+        assert (gt.lut_preset(preset) == oracle.lut(preset)).all()
+    assert gt.score_milli(11, 6, 6) == 6944 and gt.score_int(11, 6, 6) == 6     # KA1, design.md:213-217
+    rng = np.random.RandomState(3)
+    for _ in range(2000):
+        k = rng.randint(1, 17)
+        ln = k * (k - 1) // 2
+        cmax = rng.randint(0, 256)
+        s = rng.randint(0, cmax * ln + 2)
+        assert gt.score_int(s, ln, cmax) == oracle.score_int(s, ln, cmax)
+        assert gt.score_milli(s, ln, cmax) == oracle.score_milli(s, ln, cmax)
+
+
+@pytest.mark.parametrize("config,seed", [(1, 1), (2, 0x5EED0002), (3, 0x5EED0003), (33, 0x5EED0003), (4, 0x5EED0004)])
+def test_synth_cluster_matches_oracle(gt, oracle, config, seed):
+    lv, n, fr, cl, ac, sib = gt.synth_cluster(config, seed, 1000, 3000, gaia=True)
+    olv, on, ofr, ocl = oracle.synth_cluster(config, seed, 1000, 3000)
+    assert (lv == olv).all() and (n == on).all() and (fr == ofr).all() and (cl == ocl).all()
+    for cls in np.unique(cl):
+        i = int(np.nonzero(cl == cls)[0][0])
+        _, _, oac, osib = oracle.class_topology(int(cls))
+        assert (ac[i] == oac).all() and (sib[i] == osib).all()
