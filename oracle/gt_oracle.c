@@ -53,12 +53,12 @@ int gto_score_int(uint32_t sum, uint32_t len, uint32_t cmax)
 
 uint32_t gto_subset_cost(const uint8_t levels[256], const uint8_t lut[16], uint16_t mask)
 {
-    uint32_t sum = 0; int i, j;
-    for (i = 0; i < GTO_MAX_GPUS; i++) {
-        if (!((mask >> i) & 1)) continue;
-        for (j = i + 1; j < GTO_MAX_GPUS; j++)
-            if ((mask >> j) & 1) sum += lut[levels[i * 16 + j] & 15]; /* getTopology(g1,g2), design.md:169 */
-    }
+    /* ids = the chosen device list; sum over its C(k,2) pairs (design.md:208 sum(topology), len(topology) terms) */
+    int ids[GTO_MAX_GPUS], k = 0, a, b; uint32_t sum = 0, m = mask;
+    while (m) { ids[k++] = __builtin_ctz(m); m &= m - 1; }
+    for (a = 0; a < k; a++)
+        for (b = a + 1; b < k; b++)
+            sum += lut[levels[ids[a] * 16 + ids[b]] & 15];   /* getTopology(g1,g2), design.md:169 */
     return sum;
 }
 
