@@ -24,8 +24,9 @@ EXPORTS = [
     "gt_score_int", "gt_score_milli", "gt_load_nodes", "gt_update_free", "gt_score_all", "gt_score_dirty",
     "gt_best_node", "gt_allocate", "gt_commit", "gt_release", "gt_score_all_async", "gt_sync", "gt_stream",
     "gt_device_best", "gt_num_nodes", "gt_launch_count", "gt_count_subsets", "gt_time_kernel",
-    "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster",
+    "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static",
 ]
+STATIC_MAX_NODES = 4096
 
 u8p = C.POINTER(C.c_uint8)
 u16p = C.POINTER(C.c_uint16)
@@ -95,6 +96,8 @@ def _lib():
     L.gt_comm_unique_id.argtypes = [u8p]
     L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
+    L.gt_score_nodes_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
+                                        C.c_char_p, C.c_size_t]
     _LIB = L
     return L
 
@@ -132,6 +135,16 @@ def synth_cluster(config, seed, first, count, gaia=False):
     if rc:
         raise GtError(rc, "gt_synth_cluster")
     return (lv, n, fr, cl, ac, sib) if gaia else (lv, n, fr, cl)
+
+
+def score_nodes_static(d_cost, d_n_gpus, d_free_mask, n_nodes, d_best, stream=None):
+    """Allocation-free K0 + K1 on caller-owned DEVICE buffers (raw pointers); see gt_score_nodes_static
+    in include/gputopo.h for who needs this and its limits.  Enqueues only: synchronise `stream` before
+    reading d_best."""
+    buf = C.create_string_buffer(256)
+    rc = _lib().gt_score_nodes_static(d_cost, d_n_gpus, d_free_mask, n_nodes, d_best, stream, buf, len(buf))
+    if rc:
+        raise GtError(rc, "gt_score_nodes_static", buf.value.decode())
 
 
 def comm_unique_id():

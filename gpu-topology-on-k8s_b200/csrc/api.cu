@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -592,3 +593,95 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// gt_score_nodes_static: K0 + K1 with their scratch in a fixed device array (see gputopo.h).
+// Layout: 64 words of bin counters (17 used, padded to 256 B), then 17 bin lists of
+// GT_STATIC_MAX_NODES node ids each.
+static __device__ __align__(256) uint32_t g_static_scratch[64 + gt::kBins * GT_STATIC_MAX_NODES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+constexpr uint32_t kStaticCntWords = 64;
+// g_static_scratch names a host-side stand-in here, not device memory: the address a kernel may use
+// is looked up once per device with cudaGetSymbolAddress and remembered.
+uint32_t *g_static_dev_ptr[kStaticMaxDevices];
+int g_static_sms[kStaticMaxDevices];
+std::mutex g_static_mu;
+
+int static_fail(int code, char *buf, size_t len, const char *msg, const char *detail = "")
+{
+    if (buf && len) snprintf(buf, len, "%s%s", msg, detail);
+    return code;
+}
+}  // namespace
+
+extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_gpus, const uint16_t *d_free_mask,
+                                     uint32_t n_nodes, uint32_t *d_best, void *stream, char *err_buf, size_t err_len)
+{
+    if (err_buf && err_len) err_buf[0] = 0;
+    if (n_nodes > GT_STATIC_MAX_NODES) {
+        char d[96];
+        snprintf(d, sizeof d, "%u nodes requested, the built-in scratch holds at most %u", n_nodes, GT_STATIC_MAX_NODES);
+        return static_fail(GT_ERR_RANGE, err_buf, err_len, "gt_score_nodes_static: ", d);
+    }
+    if (n_nodes == 0) return GT_OK;
+    if (!d_cost || !d_n_gpus || !d_free_mask || !d_best)
+        return static_fail(GT_ERR_INVALID, err_buf, err_len, "gt_score_nodes_static: null buffer");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return static_fail(GT_ERR_NO_DEVICE, err_buf, err_len, "gt_score_nodes_static: ", cudaGetErrorString(e));
+    }
+    if (dev < 0 || dev >= kStaticMaxDevices)
+        return static_fail(GT_ERR_INVALID, err_buf, err_len, "gt_score_nodes_static: device ordinal not supported");
+    uint32_t *scratch;
+    int sms;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_dev_ptr[dev]) {   // one-time set-up for this device (it is current)
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e != cudaSuccess || !p) {
+                cudaGetLastError();
+                return static_fail(GT_ERR_CUDA, err_buf, err_len, "cudaGetSymbolAddress(g_static_scratch): ",
+                                   cudaGetErrorString(e));
+            }
+            int n_sm = 0;
+            e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+            if (e != cudaSuccess || n_sm <= 0) {
+                cudaGetLastError();
+                return static_fail(GT_ERR_CUDA, err_buf, err_len, "cudaDeviceGetAttribute: ", cudaGetErrorString(e));
+            }
+            g_static_sms[dev] = n_sm;
+            g_static_dev_ptr[dev] = static_cast<uint32_t *>(p);
+        }
+        scratch = g_static_dev_ptr[dev];
+        sms = g_static_sms[dev];
+    }
+    cudaPointerAttributes attr;
+    e = cudaPointerGetAttributes(&attr, d_best);
+    if (e != cudaSuccess || (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged) ||
+        (attr.type == cudaMemoryTypeDevice && attr.device != dev)) {
+        cudaGetLastError();
+        return static_fail(GT_ERR_INVALID, err_buf, err_len,
+                           "gt_score_nodes_static: d_best is not device memory of the current device");
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    uint32_t *cnt = scratch, *list = scratch + kStaticCntWords;
+    // the array keeps the previous call's contents: the counters must start at zero, the lists are
+    // overwritten up to the new counts
+    e = cudaMemsetAsync(cnt, 0, kStaticCntWords * sizeof(uint32_t), s);
+    if (e != cudaSuccess) return static_fail(GT_ERR_CUDA, err_buf, err_len, "cudaMemsetAsync: ", cudaGetErrorString(e));
+    gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
+                                                                     GT_STATIC_MAX_NODES, cnt, list);
+    gt::ScoreParams prm;
+    prm.cost = d_cost; prm.n_gpus = d_n_gpus; prm.free_mask = d_free_mask; prm.best = d_best;
+    prm.bin_cnt = cnt; prm.bin_list = list; prm.cap = GT_STATIC_MAX_NODES;
+    const uint32_t grid = std::min<uint32_t>(n_nodes + gt::kBins, (uint32_t)sms * 8);
+    gt::k_score<<<grid, gt::kCta, 0, s>>>(prm);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(GT_ERR_CUDA, err_buf, err_len, "kernel launch: ", cudaGetErrorString(e));
+    return GT_OK;
+}

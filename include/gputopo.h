@@ -128,6 +128,32 @@ int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds
  * CUDA events on the context's stream; out_ms = average per launch */
 int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
 
+/* ---- scoring without any allocation ---- */
+/* No counterpart in the reference.
+ * Some hosts of this library cannot allocate device memory at the moment they need a scoring pass:
+ * an extender embedded in a process whose memory pool already owns the whole GPU (cudaMalloc there
+ * fails or fragments the pool), or a latency-critical scheduling loop that cannot afford the
+ * device-wide synchronisation cudaMalloc/cudaFree imply.  For them this one call runs K0 + K1
+ * (bin by popcount, then score every k-subset) on buffers the CALLER already owns, and keeps the
+ * kernels' scratch (bin counters and bin lists, ~272 KiB) in a fixed array inside the library image:
+ * every GPU that loads libgputopo.so holds that array until the process exits.
+ *   d_cost      n_nodes x 256 u8 pair costs on the device (16x16 per node; with the default cost
+ *               table a cost equals the GT_LV_* level code, so level tiles can be passed as they are)
+ *   d_n_gpus    n_nodes u8, d_free_mask n_nodes u16, d_best n_nodes x 16 u32 (output, as gt_score_all)
+ *   stream      cudaStream_t to enqueue on (NULL = the legacy default stream); the call returns
+ *               once the work is enqueued -- synchronise the stream before reading d_best
+ * Limits and rules:
+ *   - n_nodes <= GT_STATIC_MAX_NODES, otherwise GT_ERR_RANGE (and a message in err_buf, if given);
+ *   - the device that owns the buffers must be current; the first call on each device looks up the
+ *     array's device address (one-time set-up) and should therefore happen before any stream capture;
+ *   - all calls on a device share the one array: the counters are cleared at the start of every call,
+ *     the rest is overwritten, but two calls that overlap on the GPU (different streams without an
+ *     ordering between them, or several host threads) race -- keep them stream-ordered;
+ *   - nothing here calls cudaMalloc, cudaFree or any allocating library routine. */
+#define GT_STATIC_MAX_NODES 4096u
+int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_gpus, const uint16_t *d_free_mask,
+                          uint32_t n_nodes, uint32_t *d_best, void *stream, char *err_buf, size_t err_len);
+
 /* ---- multi-GPU: nodes are sharded, one context per GPU; the only exchange is a min over 16 keys ---- */
 int gt_comm_unique_id(uint8_t out_id[128]);
 int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
