@@ -2,8 +2,8 @@
 """bench.py -- candidate GPU subsets scored per second on the topology-aware allocation path.
 
 A step is one Prioritize pass (design.md:118) over this rank's shard of a synthetic cluster:
-K0 bin -> K1 score every k-subset of every node's free set -> K2 cluster argmin per k (+ a 128-byte
-NCCL min across ranks when N > 1).  Workload: BASELINE.json config 4 (heterogeneous 100k-node
+K0 k_bin (bin nodes by popcount(free)) -> K1 k_score (score every k-subset of every node's free set, per-node
+argmin, cluster argmin folded in) (+ a 128-byte NCCL min across ranks when N > 1).  Workload: BASELINE.json config 4 (heterogeneous 100k-node
 cluster), 100 000 nodes PER GPU (weak scaling: nodes are independent).
 
     python bench.py [--gpus N] [--steps K] [--warmup W]        (torchrun for N > 1)
@@ -257,7 +257,7 @@ def main():
     roofline, kernels = None, {}
     if rank == 0:
         c = ctxs[0]
-        for name in ("bin", "score", "argmin"):
+        for name in ("step", "bin", "score", "argmin", "prioritize"):
             kernels[name + "_us"] = c.time_kernel(name, 50) * 1e3
         peak_ms = c.time_kernel("int32_peak", 5)
         sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
@@ -273,10 +273,10 @@ def main():
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_bytes = N * (256 + 2 + 64)      # BASELINE.md section 5 with n = 16 storage: matrix + mask + best row
         roofline = {
-            "kernel": "k_score", "bound": "alu", "achieved": alg_adds / t_score / 1e9, "peak": peak_adds / 1e9,
+            "kernel": "k_score (K1 + folded cluster argmin)", "bound": "alu", "achieved": alg_adds / t_score / 1e9, "peak": peak_adds / 1e9,
             "unit": "Gadd/s", "frac": (alg_adds / t_score) / peak_adds, "traffic": None,
             "note": "ALU-bound path (BASELINE.md section 5): achieved = algorithmic pair-cost additions sum C(f,2)*2^(f-2) "
-                    "per launch / k_score duration; peak = INT32 add rate measured live (k_int32_peak). The kernel does "
+                    "per launch / kernel duration; peak = INT32 add rate measured live (k_int32_peak). The kernel does "
                     "fewer real instructions than the algorithmic count (incremental tree), so frac may exceed 1.",
             "subsets_per_s_kernel": subsets[0] / t_score,
             "hbm": {"bound": "hbm", "achieved": alg_bytes / t_score / 1e9, "peak": hbm_peak, "unit": "GB/s",

@@ -18,6 +18,7 @@ NO_PLACE = 0xFFFFFFFFFFFFFFFF
 LV = dict(X=0, NVS=1, NV4=2, NV3=3, NV2=4, NV1=5, PSB=6, PIX=7, PXB=8, PHB=9, NODE=10, SYS=11)
 LUT_DEFAULT, LUT_DESIGN_MARKS = 0, 1
 K1_FIRST_UNUSED, K1_GAIA_SINGULAR = 0, 1
+FLAG_FUSED_CHUNKS = 1
 
 EXPORTS = [
     "gt_create", "gt_destroy", "gt_strerror", "gt_last_error", "gt_lut_preset", "gt_set_cost_lut",
@@ -158,9 +159,9 @@ def comm_unique_id():
 class Allocator:
     """One context = one GPU's shard of the cluster (nodes [first_node, first_node + max_nodes))."""
 
-    def __init__(self, max_nodes, device=0, first_node=0, k1_policy=K1_FIRST_UNUSED, stream=None):
+    def __init__(self, max_nodes, device=0, first_node=0, k1_policy=K1_FIRST_UNUSED, stream=None, flags=0):
         self._L = _lib()
-        cfg = GtConfig(C.sizeof(GtConfig), device, max_nodes, first_node, k1_policy, 0, stream)
+        cfg = GtConfig(C.sizeof(GtConfig), device, max_nodes, first_node, k1_policy, flags, stream)
         h = C.c_void_p()
         rc = self._L.gt_create(C.byref(cfg), C.byref(h))
         if rc:

@@ -22,7 +22,8 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return SO
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + SOURCES + ["-ldl"]
+    extra = os.environ.get("GT_NVCC_EXTRA", "").split()
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + SOURCES + ["-ldl"]
     subprocess.run(cmd, check=True)
     return SO
 

@@ -57,7 +57,7 @@ struct gt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    uint32_t cap = 0, n_nodes = 0, first_node = 0, k1_policy = 0;
+    uint32_t cap = 0, n_nodes = 0, first_node = 0, k1_policy = 0, flags = 0;
     int num_sms = 148;
     uint8_t lut[16];
     // HBM tables (SoA)
@@ -66,8 +66,12 @@ struct gt_ctx {
     uint16_t *d_sibling = nullptr;
     uint16_t *d_free = nullptr;
     uint32_t *d_best = nullptr;
-    uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1
-    unsigned long long *d_place = nullptr;
+    uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
+    uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
+    unsigned long long *d_place = nullptr;      // [3][16]: two parities of the fused kernel, [2] = binned path
+    unsigned long long *place_cur = nullptr;    // where the latest placement keys are
+    uint32_t *d_ticket = nullptr;               // [2] chunk tickets of the fused kernel
+    uint32_t parity = 0;
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
@@ -115,7 +119,7 @@ uint4 lut_as_uint4(const uint8_t lut[16])
 int apply_lut(gt_ctx *c, uint32_t first, uint32_t count)
 {
     if (!count) return GT_OK;
-    const size_t n16 = (size_t)count * 16;   // 256 B per node = 16 uint4
+    const size_t n16 = (size_t)count * 16;   // tile rows: 16 per node, 16 bytes each
     const int grid = (int)std::min<size_t>((n16 + 255) / 256, (size_t)c->num_sms * 8);
     gt::k_apply_lut<<<grid, 256, 0, c->stream>>>(c->d_levels + (size_t)first * 256, c->d_cost + (size_t)first * 256,
                                                  n16, lut_as_uint4(c->lut));
@@ -168,56 +172,90 @@ void mark_dirty(gt_ctx *c, uint32_t node)
     c->place_valid = false;
 }
 
-gt::ScoreParams score_params(gt_ctx *c)
+gt::ScoreParams score_params(gt_ctx *c, bool fold, bool keep_bins)
 {
     gt::ScoreParams p;
-    p.cost = c->d_cost; p.n_gpus = c->d_ngpus; p.free_mask = c->d_free; p.best = c->d_best;
-    p.bin_cnt = c->d_bin_cnt; p.bin_list = c->d_bin_list; p.cap = c->cap;
+    p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
+    p.bin_free = c->d_bin_free; p.place = c->d_place + 32; p.cap = c->cap; p.first_node = c->first_node;
+    p.fold_place = fold ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u;
     return p;
 }
 
-int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
+// K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, bool preset_place)
 {
-    GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kBins * sizeof(uint32_t), c->stream));
-    gt::k_bin<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(c->d_ngpus, c->d_free, d_ids, n, c->cap,
-                                                                       c->d_bin_cnt, c->d_bin_list);
+    gt::k_bin<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+        c->d_ngpus, c->d_free, d_ids, n, c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best,
+        preset_place ? c->d_place + 32 : nullptr);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     return GT_OK;
 }
 
-int launch_score(gt_ctx *c, uint32_t n)
+int launch_score(gt_ctx *c, uint32_t n, bool fold, bool keep_bins = false)
 {
-    const uint32_t grid = std::min<uint32_t>(n + gt::kBins, (uint32_t)c->num_sms * 8);
-    gt::k_score<<<grid, gt::kCta, 0, c->stream>>>(score_params(c));
+    // persistent warps: every resident CTA slot, fewer when there is little work
+    const uint32_t grid = std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::kScoreMinCtas);
+    gt::k_score<<<grid, gt::kScoreCta, 0, c->stream>>>(score_params(c, fold, keep_bins));
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
+    if (fold) c->place_cur = c->d_place + 32;
     return GT_OK;
 }
 
 int launch_argmin(gt_ctx *c)
 {
-    GT_CUDA(c, cudaMemsetAsync(c->d_place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
-    const size_t total = (size_t)c->n_nodes * 16;
-    const uint32_t grid = (uint32_t)std::min<size_t>((total + gt::kCta * 4 - 1) / (gt::kCta * 4), (size_t)c->num_sms * 4);
-    gt::k_argmin<<<std::max(grid, 1u), gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, c->first_node, c->d_place);
+    unsigned long long *place = c->d_place + 32;
+    GT_CUDA(c, cudaMemsetAsync(place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
+    const size_t quarters = (size_t)c->n_nodes * 4;      // 16-byte pieces; 8 per thread
+    const uint32_t grid = (uint32_t)std::min<size_t>((quarters + gt::kCta * 8 - 1) / (gt::kCta * 8), (size_t)c->num_sms * 4);
+    gt::k_argmin<<<std::max(grid, 1u), gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, c->first_node, place);
+    c->place_cur = place;
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     return GT_OK;
 }
 
-// K0 + K1 over `n` nodes (all, or the listed ones), then K2 over the whole table
+// the fused kernel: K0 + K1 + K2 of every loaded node in one launch
+int launch_prioritize(gt_ctx *c)
+{
+    gt::PrioParams p;
+    p.cost = c->d_cost; p.n_gpus = c->d_ngpus; p.free_mask = c->d_free; p.best = c->d_best;
+    p.place = c->d_place; p.ticket = c->d_ticket;
+    p.n_nodes = c->n_nodes; p.first_node = c->first_node; p.parity = c->parity;
+    const uint32_t chunks = (c->n_nodes + gt::kChunk - 1) / gt::kChunk;
+    const uint32_t grid = std::max(1u, std::min<uint32_t>(chunks, (uint32_t)c->num_sms * 4));
+    gt::k_prioritize<<<grid, gt::kChunk, 0, c->stream>>>(p);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    c->place_cur = c->d_place + c->parity * 16;
+    c->parity ^= 1u;
+    return GT_OK;
+}
+
+// Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1 (or, with
+// GT_FLAG_FUSED_CHUNKS, the single-launch chunk kernel).  Listed (dirty) nodes: K0 + K1 over the list,
+// then K2 over the whole table.  n == 0: K2 only.
 int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
     int rc;
-    if (n) {
-        if ((rc = launch_bin(c, d_ids, n)) != GT_OK) return rc;
-        if ((rc = launch_score(c, n)) != GT_OK) return rc;
+    if (!d_ids && n) {
+        if (c->flags & GT_FLAG_FUSED_CHUNKS) {
+            if ((rc = launch_prioritize(c)) != GT_OK) return rc;
+        } else {
+            if ((rc = launch_bin(c, nullptr, n, true)) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, true)) != GT_OK) return rc;
+        }
+    } else {
+        if (n) {
+            if ((rc = launch_bin(c, d_ids, n, false)) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, false)) != GT_OK) return rc;
+        }
+        if ((rc = launch_argmin(c)) != GT_OK) return rc;
     }
-    if ((rc = launch_argmin(c)) != GT_OK) return rc;
     if (c->comm) {
         NcclApi *api = nccl_api();
-        int e = api->AllReduce(c->d_place, c->d_place, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
+        int e = api->AllReduce(c->place_cur, c->place_cur, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
         if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     }
     c->best_valid = true;
@@ -264,6 +302,7 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
     c->cap = cfg->max_nodes;
     c->first_node = cfg->first_node;
     c->k1_policy = cfg->k1_policy;
+    c->flags = cfg->flags;
     gt_lut_preset(GT_LUT_DEFAULT, c->lut);
     int rc = [&]() -> int {
         GT_CUDA(c, cudaSetDevice(c->device));
@@ -284,9 +323,15 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_sibling, N * 32));
         GT_CUDA(c, cudaMalloc(&c->d_free, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_best, N * 64));
-        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, gt::kBins * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_free, (size_t)gt::kBins * N * sizeof(uint16_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMalloc(&c->d_place, 16 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMalloc(&c->d_place, 48 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 48 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMalloc(&c->d_ticket, 2 * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMemset(c->d_ticket, 0, 2 * sizeof(uint32_t)));
+        c->place_cur = c->d_place + 32;
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
@@ -326,8 +371,8 @@ void gt_destroy(gt_ctx *c)
         if (api) api->CommDestroy(c->comm);
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
-    cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_place);
-    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out);
+    cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_place);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_ticket);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
@@ -475,7 +520,7 @@ int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place
         int rc = enqueue_scoring(c, nullptr, 0);
         if (rc != GT_OK) return rc;
     }
-    GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->d_place, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
     for (uint32_t i = 0; i < nreq; i++)
         out_place[i] = (k[i] >= 1 && k[i] <= 16) ? (uint64_t)c->h_place[k[i] - 1] : GT_NO_PLACE;
@@ -530,9 +575,17 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     const std::string w(which);
     const uint32_t peak_iters = 2048;
     auto one = [&]() -> int {
-        if (w == "bin") return launch_bin(c, nullptr, c->n_nodes);
-        if (w == "score") return launch_score(c, c->n_nodes);
+        if (w == "bin") {   // K0 alone: its counters have to be cleared by hand between launches
+            GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
+            return launch_bin(c, nullptr, c->n_nodes, true);
+        }
+        if (w == "score") return launch_score(c, c->n_nodes, true, true);
         if (w == "argmin") return launch_argmin(c);
+        if (w == "prioritize") return launch_prioritize(c);
+        if (w == "step") return enqueue_scoring(c, nullptr, c->n_nodes);
+        if (w == "noop") { gt::k_noop<<<1, 32, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
+        if (w == "noop_grid") { gt::k_noop<<<c->num_sms * 4, 128, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
+        if (w == "noop_smem") { gt::k_noop_smem<<<c->num_sms * 4, 128, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
         if (w == "int32_peak") {
             gt::k_int32_peak<<<c->num_sms * 8, gt::kCta, 0, c->stream>>>(c->d_peak_out, peak_iters, 12345u);
             c->launches++;
@@ -541,8 +594,8 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
         return GT_ERR_INVALID;
     };
     if (w == "score" || w == "argmin") {   // bins / best table must exist
-        if ((rc = launch_bin(c, nullptr, c->n_nodes)) != GT_OK) return rc;
-        if ((rc = launch_score(c, c->n_nodes)) != GT_OK) return rc;
+        if ((rc = launch_bin(c, nullptr, c->n_nodes, true)) != GT_OK) return rc;
+        if ((rc = launch_score(c, c->n_nodes, true, true)) != GT_OK) return rc;
     }
     if ((rc = one()) != GT_OK) return rc;   // warm-up
     GT_CUDA(c, cudaEventRecord(e0, c->stream));
@@ -554,11 +607,10 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     GT_CUDA(c, cudaEventElapsedTime(&ms, e0, e1));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
-    if (w == "bin") {   // leave the pipeline consistent
-        if ((rc = launch_score(c, c->n_nodes)) != GT_OK) return rc;
-        GT_CUDA(c, cudaStreamSynchronize(c->stream));
-        c->best_valid = true;
-    }
+    // leave the pipeline consistent: control block zero, best table and placement keys current
+    GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
+    if ((rc = enqueue_scoring(c, nullptr, c->n_nodes)) != GT_OK) return rc;
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
     *out_ms = ms / (float)iters;
     return GT_OK;
 }
@@ -596,9 +648,9 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
 
 // ------------------------------------------------------------------------------------------------
 // gt_score_nodes_static: K0 + K1 with their scratch in a fixed device array (see gputopo.h).
-// Layout: 64 words of bin counters (17 used, padded to 256 B), then 17 bin lists of
-// GT_STATIC_MAX_NODES node ids each.
-static __device__ __align__(256) uint32_t g_static_scratch[64 + gt::kBins * GT_STATIC_MAX_NODES];
+// Layout: 64 words of control block (bin counters, K1 ticket; padded to 256 B), then 17 bin lists of
+// GT_STATIC_MAX_NODES node ids (u32) each, then the same lists' free masks (u16).
+static __device__ __align__(256) uint32_t g_static_scratch[64 + gt::kBins * GT_STATIC_MAX_NODES + gt::kBins * GT_STATIC_MAX_NODES / 2];
 
 namespace {
 constexpr int kStaticMaxDevices = 64;
@@ -674,13 +726,15 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     // overwritten up to the new counts
     e = cudaMemsetAsync(cnt, 0, kStaticCntWords * sizeof(uint32_t), s);
     if (e != cudaSuccess) return static_fail(GT_ERR_CUDA, err_buf, err_len, "cudaMemsetAsync: ", cudaGetErrorString(e));
+    uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
-                                                                     GT_STATIC_MAX_NODES, cnt, list);
+                                                                     GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
+                                                                     nullptr);
     gt::ScoreParams prm;
-    prm.cost = d_cost; prm.n_gpus = d_n_gpus; prm.free_mask = d_free_mask; prm.best = d_best;
-    prm.bin_cnt = cnt; prm.bin_list = list; prm.cap = GT_STATIC_MAX_NODES;
-    const uint32_t grid = std::min<uint32_t>(n_nodes + gt::kBins, (uint32_t)sms * 8);
-    gt::k_score<<<grid, gt::kCta, 0, s>>>(prm);
+    prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
+    prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0;
+    const uint32_t grid = std::min<uint32_t>(n_nodes / 8 + gt::kBins, (uint32_t)sms * gt::kScoreMinCtas);
+    gt::k_score<<<grid, gt::kScoreCta, 0, s>>>(prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(GT_ERR_CUDA, err_buf, err_len, "kernel launch: ", cudaGetErrorString(e));
     return GT_OK;

@@ -26,67 +26,96 @@ constexpr int kMaxG = 16;
 constexpr int kBins = 17;            // popcount 0..16
 constexpr int kCta = 256;
 constexpr uint32_t kInf = 0xFFFF0000u;
-constexpr int kBigSlots = 128;       // nodes per CTA unit at p = 9 (2 lanes per node)
-constexpr int kSlotStride = 264;     // bytes per compressed cost tile in shared memory (256 + pad)
+constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
+#ifndef GT_SCORE_MIN_CTAS
+#define GT_SCORE_MIN_CTAS 4
+#endif
+constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the register budget is set for
+constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
+constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 16: shifts banks between tiles)
+constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
 
 struct ScoreParams {
     const uint8_t *cost;      // [N][256] u8 pair cost, row-major 16x16
-    const uint8_t *n_gpus;    // [N]
-    const uint16_t *free_mask;// [N]
     uint32_t *best;           // [N][16]
-    const uint32_t *bin_cnt;  // [17]
-    const uint32_t *bin_list; // [17][cap]
-    uint32_t cap;
+    uint32_t *ctl;            // control block, see kCtl*
+    const uint32_t *bin_list; // [17][cap] node ids by p
+    const uint16_t *bin_free; // [17][cap] their free masks (already limited to n_gpus bits)
+    unsigned long long *place;// [16] cluster argmin, folded into when fold_place != 0
+    uint32_t cap, first_node;
+    uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
+    uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
 };
+// scratch control block (u32 words): [0..16] bin counts, [17] K1 unit ticket, [18] K1 finished CTAs.
+// All zero between scoring passes: K1's last CTA clears it.
+constexpr int kCtlWords = 32;
+constexpr int kCtlTicket = 17, kCtlDone = 18;
 
 // ---------------------------------------------------------------- load time
-__global__ void k_apply_lut(const uint8_t *__restrict__ levels, uint8_t *__restrict__ cost, size_t n_bytes16,
+// cost[i][j] = cost[j][i] = lut[levels[min(i,j)][max(i,j)]], cost[i][i] = 0: the upper triangle of the level
+// matrix is the one that counts (gputopo.h), and the scoring kernels rely on symmetric tiles with a
+// zero diagonal (row sums over a GPU mask then equal pair sums).  One thread per tile row.
+__global__ void k_apply_lut(const uint8_t *__restrict__ levels, uint8_t *__restrict__ cost, size_t n_rows,
                             uint4 lut4)
 {
     __shared__ uint8_t s_lut[16];
     if (threadIdx.x < 4) reinterpret_cast<uint32_t *>(s_lut)[threadIdx.x] = (&lut4.x)[threadIdx.x];
     __syncthreads();
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n_bytes16; i += stride) {
-        uint4 v = reinterpret_cast<const uint4 *>(levels)[i];
-        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; r < n_rows; r += stride) {
+        const uint8_t *tile = levels + (r >> 4) * 256;
+        const uint32_t i = (uint32_t)(r & 15);
+        uint32_t w[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            uint32_t x = w[q];
-            w[q] = (uint32_t)s_lut[x & 15] | ((uint32_t)s_lut[(x >> 8) & 15] << 8) |
-                   ((uint32_t)s_lut[(x >> 16) & 15] << 16) | ((uint32_t)s_lut[(x >> 24) & 15] << 24);
+        for (uint32_t j = 0; j < 16; j++) {
+            const uint32_t lo = min(i, j), hi = max(i, j);
+            const uint32_t v = (i == j) ? 0u : (uint32_t)s_lut[tile[lo * 16 + hi] & 15];
+            w[j >> 2] |= v << ((j & 3) * 8);
         }
-        reinterpret_cast<uint4 *>(cost)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<uint4 *>(cost)[r] = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 
 // ---------------------------------------------------------------- K0: bin nodes by popcount(free)
-// ids == nullptr: nodes [0, n); else the listed (dirty) nodes.
+// ids == nullptr: nodes [0, n); else the listed (dirty) nodes.  ctl[0..16] must be zero on entry.
+// place != nullptr: preset the cluster argmin that K1 folds into.
 __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus,
                                               const uint16_t *__restrict__ free_mask,
                                               const uint32_t *__restrict__ ids, uint32_t n, uint32_t cap,
-                                              uint32_t *__restrict__ bin_cnt, uint32_t *__restrict__ bin_list)
+                                              uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
+                                              uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
+                                              unsigned long long *__restrict__ place)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
     if (tid < kBins) s_cnt[tid] = 0;
+    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
     int p = -1;
-    uint32_t slot = 0, node = 0;
+    uint32_t slot = 0, node = 0, f = 0;
     if (i < n) {
         node = ids ? ids[i] : i;
         uint32_t ng = n_gpus[node];
         ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-        const uint32_t f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
+        f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
         p = __popc(f);
         slot = atomicAdd(&s_cnt[p], 1u);
+        if (p >= kSplitP) {   // several warp units of K1 meet in this row through atomicMin
+            uint4 *o = reinterpret_cast<uint4 *>(best + (size_t)node * 16);
+            const uint4 inf = make_uint4(kInf, kInf, kInf, kInf);
+            o[0] = inf; o[1] = inf; o[2] = inf; o[3] = inf;
+        }
     }
     __syncthreads();
-    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&bin_cnt[tid], s_cnt[tid]);
+    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&ctl[tid], s_cnt[tid]);
     __syncthreads();
-    if (p >= 0) bin_list[(size_t)p * cap + s_base[p] + slot] = node;
+    if (p >= 0) {
+        const size_t at = (size_t)p * cap + s_base[p] + slot;
+        bin_list[at] = node;
+        bin_free[at] = (uint16_t)f;
+    }
 }
 
 // ---------------------------------------------------------------- the unrolled subset tree
@@ -122,15 +151,9 @@ struct Children {   // children of S add a position in [0, B)
 
 // ---------------------------------------------------------------- K1 small: one thread per node, p == P <= 8
 template <int P>
-__device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t node)
+__device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t node, uint32_t f, uint32_t (&out)[16])
 {
-    uint32_t out[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) out[k] = kInf;
     if constexpr (P > 0) {
-        uint32_t ng = prm.n_gpus[node];
-        ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-        uint32_t f = (uint32_t)prm.free_mask[node] & ((1u << ng) - 1u);
         uint32_t pos[P], bit[P];
 #pragma unroll
         for (int a = 0; a < P; a++) {
@@ -155,156 +178,259 @@ __device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t nod
 #pragma unroll
         for (int k = 1; k <= P; k++) out[k - 1] = acc[k];
     }
-    uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)node * 16);
-    o[0] = make_uint4(out[0], out[1], out[2], out[3]);
-    o[1] = make_uint4(out[4], out[5], out[6], out[7]);
-    o[2] = make_uint4(out[8], out[9], out[10], out[11]);
-    o[3] = make_uint4(out[12], out[13], out[14], out[15]);
+}
+
+// lowest (cost, node) of a warp's candidates for request size k+1 -> one shared-memory atomicMin
+__device__ __forceinline__ void fold_place_warp(unsigned long long *s_place, int k, uint32_t v, uint32_t node,
+                                                uint32_t first_node)
+{
+    const uint32_t cmin = __reduce_min_sync(0xFFFFFFFFu, v & 0xFFFF0000u);
+    if (cmin != kInf) {   // warp-uniform
+        const uint32_t cand = ((v & 0xFFFF0000u) == cmin) ? node : 0xFFFFFFFFu;
+        const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, cand);
+        if (node == nmin && (v & 0xFFFF0000u) == cmin) {
+            const unsigned long long key = ((unsigned long long)(cmin >> 16) << 48) |
+                                           ((unsigned long long)(first_node + node) << 16) | (v & 0xFFFFu);
+            atomicMin(&s_place[k], key);
+        }
+    }
 }
 
 // ---------------------------------------------------------------- K1 big: p > 8, 2^(p-8) lanes per node
-struct BigSmem {
-    uint8_t cc[kBigSlots * kSlotStride];   // compressed pair costs cc[slot][a*16+b], symmetric
-    uint16_t bit[kBigSlots][16];           // 1 << gpu index of compressed position a (0 beyond p)
-    uint32_t best[kBigSlots][kBins];       // per k minima of the slot's node
-    uint32_t node[kBigSlots];
-};
-
-__device__ __forceinline__ void score_big(const ScoreParams &prm, BigSmem &sm, int p, uint32_t unit,
-                                          uint32_t cnt)
+// 4 bits -> 4 bytes of 0xFF
+__device__ __forceinline__ uint32_t bytemask4(uint32_t nib)
 {
-    const uint32_t tid = threadIdx.x;
-    const int hb = p - 8;                       // bits of H
-    const uint32_t slots = (uint32_t)kCta >> hb; // nodes in this unit
-    const uint32_t first = unit * slots;
-    const uint32_t live = min(slots, cnt - first);
-    const uint32_t npairs = (uint32_t)(p * (p - 1) / 2);
-
-    // positions of the free GPUs, per slot
-    if (tid < live) {
-        const uint32_t node = prm.bin_list[(size_t)p * prm.cap + first + tid];
-        sm.node[tid] = node;
-        uint32_t ng = prm.n_gpus[node];
-        ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-        uint32_t f = (uint32_t)prm.free_mask[node] & ((1u << ng) - 1u);
-#pragma unroll
-        for (int a = 0; a < 16; a++) {
-            const int g = f ? __ffs(f) - 1 : 0;
-            f &= f - 1;
-            sm.bit[tid][a] = (a < p) ? (uint16_t)(1u << g) : (uint16_t)0;
-        }
-    }
-    for (uint32_t e = tid; e < live * kBins; e += kCta) sm.best[e / kBins][e % kBins] = kInf;
-    __syncthreads();
-    // compressed pair costs: pairs ordered (0,1),(0,2),(1,2),(0,3),... so the first C(p,2) cover positions < p
-    for (uint32_t e = tid; e < live * npairs; e += kCta) {
-        const uint32_t s = e / npairs, q = e - s * npairs;
-        // b = largest with b(b-1)/2 <= q
-        uint32_t b = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
-        while (b * (b - 1) / 2 > q) b--;
-        while ((b + 1) * b / 2 <= q) b++;
-        const uint32_t a = q - b * (b - 1) / 2;
-        const uint32_t ga = __ffs((uint32_t)sm.bit[s][a]) - 1, gb = __ffs((uint32_t)sm.bit[s][b]) - 1;
-        const uint8_t v = __ldg(prm.cost + (size_t)sm.node[s] * 256 + ga * 16 + gb);
-        sm.cc[s * kSlotStride + a * 16 + b] = v;
-        sm.cc[s * kSlotStride + b * 16 + a] = v;
-    }
-    __syncthreads();
-
-    const uint32_t slot = tid >> hb;
-    const uint32_t h = tid & ((1u << hb) - 1u);
-    if (slot < live) {
-        const uint8_t *cc = sm.cc + slot * kSlotStride;
-        uint32_t c[64], bit[8], R[8], acc[9];
-#pragma unroll
-        for (int a = 0; a < 8; a++) {
-            bit[a] = sm.bit[slot][a];
-#pragma unroll
-            for (int b = 0; b < 8; b++) c[a * 8 + b] = (a < b) ? ((uint32_t)cc[a * 16 + b] << 16) : 0u;
-        }
-        uint32_t ch = 0, hmask = 0;
-#pragma unroll
-        for (int b = 0; b < 8; b++) R[b] = 0u;
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            if ((h >> j) & 1u) {
-                hmask += sm.bit[slot][8 + j];
-#pragma unroll
-                for (int b = 0; b < 8; b++) R[b] += (uint32_t)cc[b * 16 + 8 + j];
-#pragma unroll
-                for (int i = 0; i < 8; i++)
-                    if (i < j && ((h >> i) & 1u)) ch += (uint32_t)cc[(8 + i) * 16 + 8 + j];
-            }
-        }
-#pragma unroll
-        for (int b = 0; b < 8; b++) R[b] <<= 16;
-        const uint32_t key0 = (ch << 16) | hmask;
-#pragma unroll
-        for (int k = 0; k <= 8; k++) acc[k] = kInf;
-        if (h) acc[0] = key0;
-        Children<8, 8, 0>::run(key0, R, c, bit, acc);
-        const int o = __popc(h);
-#pragma unroll
-        for (int j = 0; j <= 8; j++)
-            if (acc[j] != kInf) atomicMin(&sm.best[slot][o + j], acc[j]);
-    }
-    __syncthreads();
-    for (uint32_t e = tid; e < live * 16; e += kCta) {
-        const uint32_t s = e >> 4, k = (e & 15u) + 1u;
-        prm.best[(size_t)sm.node[s] * 16 + (k - 1)] = sm.best[s][k];
-    }
-    __syncthreads();
+    return ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
+}
+// sum of the bytes of a tile row selected by a byte mask
+__device__ __forceinline__ uint32_t row_sum(const uint4 row, const uint32_t (&m)[4])
+{
+    uint32_t s = __dp4a(row.x & m[0], 0x01010101u, 0u);
+    s = __dp4a(row.y & m[1], 0x01010101u, s);
+    s = __dp4a(row.z & m[2], 0x01010101u, s);
+    return __dp4a(row.w & m[3], 0x01010101u, s);
 }
 
-// Work units of 256 lanes, heaviest bins first: bin p > 8 has cnt*2^(p-8) lanes, bin p <= 8 has cnt.
-__global__ void __launch_bounds__(kCta, 2) k_score(ScoreParams prm)
+// one lane of a big node: subsets H (given by h over the free GPUs beyond the 8 lowest) x the 8-position tree.
+// raw: the node's 16x16 cost tile in shared memory, symmetric, zero diagonal, 16-byte aligned.
+__device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, int hb, uint32_t h, uint32_t *best_row)
 {
-    __shared__ BigSmem sm;
+    uint32_t pos[8], bit[8], c[64], R[8], acc[9];
+#pragma unroll
+    for (int a = 0; a < 8; a++) {
+        const int g = __ffs(f) - 1;
+        f &= f - 1;
+        pos[a] = (uint32_t)g;
+        bit[a] = 1u << g;
+    }
+    // H = the free GPUs beyond the 8 lowest whose bit in h is set
+    uint32_t hmask = 0;
+    for (int j = 0; j < hb; j++) {
+        const uint32_t low = f & (0u - f);
+        f ^= low;
+        if ((h >> j) & 1u) hmask |= low;
+    }
+    uint32_t m[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) m[q] = bytemask4((hmask >> (4 * q)) & 15u);
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+        for (int b = 0; b < 8; b++)
+            c[a * 8 + b] = (a < b) ? ((uint32_t)raw[pos[a] * 16 + pos[b]] << 16) : 0u;
+    // cross cost of tree position b against H, and the cost inside H (each pair counted twice)
+#pragma unroll
+    for (int b = 0; b < 8; b++)
+        R[b] = row_sum(*reinterpret_cast<const uint4 *>(raw + pos[b] * 16), m) << 16;
+    uint32_t ch2 = 0;
+    for (uint32_t hm = hmask; hm; hm &= hm - 1)
+        ch2 += row_sum(*reinterpret_cast<const uint4 *>(raw + (__ffs(hm) - 1) * 16), m);
+    const int nsel = __popc(h);
+    const uint32_t key0 = ((ch2 >> 1) << 16) | hmask;
+#pragma unroll
+    for (int k = 0; k <= 8; k++) acc[k] = kInf;
+    if (h) acc[0] = key0;
+    Children<8, 8, 0>::run(key0, R, c, bit, acc);
+#pragma unroll
+    for (int j = 0; j <= 8; j++)
+        if (acc[j] != kInf) atomicMin(best_row + nsel + j, acc[j]);
+}
+
+// Warp-private staging: the 16x16 cost tiles of the unit's nodes (coalesced 16-byte loads) and the
+// per-k minima of each node.  No CTA barrier in K1's work loop.
+struct WarpScratch {
+    __align__(16) uint8_t raw[kTilesPerWarp * kTileStride];
+    uint32_t best[kTilesPerWarp][kBins];
+};
+
+// hb = p - 8 bits of H.  hb <= 5: a warp holds 32 >> hb nodes.  hb > 5: a node spans 2^(hb-5) warp units
+// whose minima meet in global memory (rows preset to kInf by k_bin).
+__device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScratch &ws, unsigned long long *s_place,
+                                               int p, uint32_t lu, uint32_t cnt, uint32_t lane)
+{
+    const int hb = p - 8;
+    const uint32_t *list = prm.bin_list + (size_t)p * prm.cap;
+    const uint16_t *flist = prm.bin_free + (size_t)p * prm.cap;
+    uint32_t first, live, slot, h;
+    if (hb <= 5) {
+        const uint32_t slots = 32u >> hb;
+        first = lu * slots;
+        live = min(slots, cnt - first);
+        slot = lane >> hb;
+        h = lane & ((1u << hb) - 1u);
+    } else {
+        first = lu >> (hb - 5);
+        live = 1;
+        slot = 0;
+        h = ((lu & ((1u << (hb - 5)) - 1u)) << 5) | lane;
+    }
+    const bool active = slot < live;
+    const uint32_t node = __ldg(list + first + (active ? slot : 0u));
+    const uint32_t f = __ldg(flist + first + (active ? slot : 0u));
+    // stage tiles: 16 lanes x 16 B per tile, two tiles per pass
+    for (uint32_t t = lane >> 4; t < live; t += 2) {
+        const uint32_t nd = __ldg(list + first + t);
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(prm.cost + (size_t)nd * 256) + (lane & 15u));
+        *reinterpret_cast<uint4 *>(ws.raw + t * kTileStride + (lane & 15u) * 16) = v;
+    }
+    for (uint32_t s2 = 0; s2 < live; s2++)
+        if (lane < (uint32_t)kBins) ws.best[s2][lane] = kInf;
+    __syncwarp();
+    if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
+    __syncwarp();
+    if (hb <= 5) {
+        // lanes 0..15 of each half-warp write one row per pass: row of slot s2, k = (lane & 15) + 1
+        for (uint32_t s2 = lane >> 4; s2 < ((live + 1u) & ~1u); s2 += 2) {
+            const bool ok = s2 < live;
+            const uint32_t nd = __ldg(list + first + (ok ? s2 : 0u));
+            const uint32_t v = ok ? ws.best[s2][(lane & 15u) + 1u] : kInf;
+            if (ok) prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+            if (prm.fold_place) {   // both half-warps hold candidates for k = (lane & 15) + 1
+                const uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, nd, 16);
+                const bool mine = (v >> 16) < (o >> 16) || ((v >> 16) == (o >> 16) && nd <= on);
+                if (lane < 16) {
+                    const uint32_t bv = mine ? v : o, bn = mine ? nd : on;
+                    if (bv != kInf) {
+                        const unsigned long long key = ((unsigned long long)(bv >> 16) << 48) |
+                            ((unsigned long long)(prm.first_node + bn) << 16) | (bv & 0xFFFFu);
+                        atomicMin(&s_place[lane], key);
+                    }
+                }
+            }
+        }
+    } else if (lane < 16) {
+        const uint32_t v = ws.best[0][lane + 1];
+        if (v != kInf) {
+            atomicMin(prm.best + (size_t)node * 16 + lane, v);
+            if (prm.fold_place) {   // a partial minimum of the node is still a valid upper bound of its key... but
+                // only the node's true minimum may enter the argmin: fold partials -- the minimum over all of the
+                // node's warp units equals the node's row, and min is associative
+                const unsigned long long key = ((unsigned long long)(v >> 16) << 48) |
+                    ((unsigned long long)(prm.first_node + node) << 16) | (v & 0xFFFFu);
+                atomicMin(&s_place[lane], key);
+            }
+        }
+    }
+    __syncwarp();
+}
+
+// Persistent warps pull work units (heaviest bins first) from a global ticket, fetching the next ticket
+// before working on the current unit.
+//   bin p <= 8 : 32 nodes per unit (one lane each)
+//   bin 9..13  : 32 >> (p-8) nodes per unit
+//   bin >= 14  : 2^(p-13) units per node
+__global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams prm)
+{
+    __shared__ WarpScratch s_ws[kScoreCta / 32];
+    __shared__ unsigned long long s_place[16];
     __shared__ uint32_t s_cnt[kBins], s_end[kBins];   // s_end[i]: cumulative units after bin p = 16 - i
-    const uint32_t tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid < 16) s_place[tid] = ~0ull;
+    if (tid < kBins) s_cnt[tid] = prm.ctl[tid];
+    __syncthreads();
     if (tid == 0) {
         uint32_t run = 0;
         for (int i = 0; i < kBins; i++) {
             const int p = 16 - i;
-            const uint32_t cnt = prm.bin_cnt[p];
-            s_cnt[p] = cnt;
-            const uint32_t per = p > 8 ? ((uint32_t)kCta >> (p - 8)) : (uint32_t)kCta;
-            run += (cnt + per - 1) / per;
+            const uint32_t cnt = s_cnt[p];
+            if (p >= kSplitP) run += cnt << (p - 13);
+            else if (p > 8) run += (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
+            else run += (cnt + 31u) >> 5;
             s_end[i] = run;
         }
     }
     __syncthreads();
     const uint32_t total = s_end[kBins - 1];
-    for (uint32_t u = blockIdx.x; u < total; u += gridDim.x) {
+    WarpScratch &ws = s_ws[warp];
+    // first unit = this warp's global index; later ones come from the ticket, requested one unit ahead
+    // (plain PTX atom: the compiler's warp-aggregated atomicAdd would wait for the reply right away)
+    const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
+    uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
+    while (u < total) {
+        uint32_t next = 0;
+        if (lane == 0)
+            asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket) : "memory");
+        next += n_warps;
         int i = 0;
         while (u >= s_end[i]) i++;
         const int p = 16 - i;
         const uint32_t lu = u - (i ? s_end[i - 1] : 0u);
         const uint32_t cnt = s_cnt[p];
         if (p > 8) {
-            score_big(prm, sm, p, lu, cnt);
+            score_big_warp(prm, ws, s_place, p, lu, cnt, lane);
         } else {
-            const uint32_t idx = lu * kCta + tid;
-            if (idx < cnt) {
-                const uint32_t node = prm.bin_list[(size_t)p * prm.cap + idx];
+            const uint32_t idx = lu * 32u + lane;
+            const bool ok = idx < cnt;
+            uint32_t out[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) out[k] = kInf;
+            uint32_t node = 0xFFFFFFFFu;
+            if (ok) {
+                const size_t at = (size_t)p * prm.cap + idx;
+                node = __ldg(prm.bin_list + at);
+                const uint32_t f = __ldg(prm.bin_free + at);
                 switch (p) {
-                case 0: score_small<0>(prm, node); break;
-                case 1: score_small<1>(prm, node); break;
-                case 2: score_small<2>(prm, node); break;
-                case 3: score_small<3>(prm, node); break;
-                case 4: score_small<4>(prm, node); break;
-                case 5: score_small<5>(prm, node); break;
-                case 6: score_small<6>(prm, node); break;
-                case 7: score_small<7>(prm, node); break;
-                default: score_small<8>(prm, node); break;
+                case 1: score_small<1>(prm, node, f, out); break;
+                case 2: score_small<2>(prm, node, f, out); break;
+                case 3: score_small<3>(prm, node, f, out); break;
+                case 4: score_small<4>(prm, node, f, out); break;
+                case 5: score_small<5>(prm, node, f, out); break;
+                case 6: score_small<6>(prm, node, f, out); break;
+                case 7: score_small<7>(prm, node, f, out); break;
+                case 8: score_small<8>(prm, node, f, out); break;
+                default: break;
                 }
+                uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)node * 16);
+                o[0] = make_uint4(out[0], out[1], out[2], out[3]);
+                o[1] = make_uint4(out[4], out[5], out[6], out[7]);
+                o[2] = make_uint4(kInf, kInf, kInf, kInf);
+                o[3] = make_uint4(kInf, kInf, kInf, kInf);
             }
+            if (prm.fold_place) {
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (k < p) fold_place_warp(s_place, k, out[k], node, prm.first_node);
+            }
+        }
+        u = __shfl_sync(0xFFFFFFFFu, next, 0);
+    }
+    __syncthreads();
+    if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
+    // the last CTA to finish leaves the control block zeroed for the next pass
+    if (tid == 0) {
+        const uint32_t done = atomicAdd(prm.ctl + kCtlDone, 1u);
+        if (done == gridDim.x - 1) {
+            if (!prm.keep_bins)
+                for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
+            prm.ctl[kCtlTicket] = 0u;
+            prm.ctl[kCtlDone] = 0u;
         }
     }
 }
 
 // ---------------------------------------------------------------- K2: best node per k
-// ids == nullptr: all nodes [0, n).  place[16] must hold ~0 (or a previous partial minimum) on entry.
+// place[16] must hold ~0 (or a previous partial minimum) on entry.  Each thread reads whole 16-byte
+// quarters of rows, so its four k are fixed: k = 4*(tid&3) + {1,2,3,4}.
 __global__ void __launch_bounds__(kCta) k_argmin(const uint32_t *__restrict__ best, uint32_t n,
                                                  uint32_t first_node, unsigned long long *__restrict__ place)
 {
@@ -312,25 +438,234 @@ __global__ void __launch_bounds__(kCta) k_argmin(const uint32_t *__restrict__ be
     const uint32_t tid = threadIdx.x;
     if (tid < 16) s_min[tid] = ~0ull;
     __syncthreads();
-    const uint32_t k = tid & 15u;
-    unsigned long long m = ~0ull;
-    const size_t total = (size_t)n * 16;
-    for (size_t e = (size_t)blockIdx.x * kCta + tid; e < total; e += (size_t)gridDim.x * kCta) {
-        const uint32_t b = best[e];
-        if (b != kInf) {
-            const unsigned long long node = first_node + (uint32_t)(e >> 4);
-            const unsigned long long key = ((unsigned long long)(b >> 16) << 48) | (node << 16) | (b & 0xFFFFu);
-            m = key < m ? key : m;
+    unsigned long long m[4] = {~0ull, ~0ull, ~0ull, ~0ull};
+    const size_t total = (size_t)n * 4;   // uint4 quarters
+    const uint4 *b4 = reinterpret_cast<const uint4 *>(best);
+    const size_t stride = (size_t)gridDim.x * kCta;
+    size_t e = (size_t)blockIdx.x * kCta + tid;
+    auto take = [&](const uint4 &v, size_t idx) {
+        const unsigned long long node = ((unsigned long long)(first_node + (uint32_t)(idx >> 2))) << 16;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const unsigned long long key = ((unsigned long long)(w[q] >> 16) << 48) | node | (w[q] & 0xFFFFu);
+            if (w[q] != kInf && key < m[q]) m[q] = key;
+        }
+    };
+    for (; e + 3 * stride < total; e += 4 * stride) {   // four independent 16-byte loads in flight
+        const uint4 v0 = __ldg(b4 + e), v1 = __ldg(b4 + e + stride), v2 = __ldg(b4 + e + 2 * stride),
+                    v3 = __ldg(b4 + e + 3 * stride);
+        take(v0, e); take(v1, e + stride); take(v2, e + 2 * stride); take(v3, e + 3 * stride);
+    }
+    for (; e < total; e += stride) take(__ldg(b4 + e), e);
+    // lanes with equal (lane & 3) hold the same four k
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+#pragma unroll
+        for (int sh = 16; sh >= 4; sh >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, m[q], sh);
+            m[q] = o < m[q] ? o : m[q];
         }
     }
-    // lanes l and l^16 hold the same k
-    {
-        const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, m, 16);
-        m = o < m ? o : m;
+    if ((tid & 31u) < 4u) {
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            if (m[q] != ~0ull) atomicMin(&s_min[(tid & 3u) * 4 + q], m[q]);
     }
-    if ((tid & 31u) < 16u && m != ~0ull) atomicMin(&s_min[k], m);
     __syncthreads();
     if (tid < 16 && s_min[tid] != ~0ull) atomicMin(&place[tid], s_min[tid]);
+}
+
+// ---------------------------------------------------------------- fused Prioritize: K0 + K1 + K2 in one launch
+// A CTA takes a chunk of 128 consecutive nodes: stages their cost tiles in shared memory with
+// coalesced 16-byte loads, sorts the chunk by p = popcount(free) (big nodes first, p descending), runs
+// the lane-per-subset-group enumeration for p > 8 and the thread-per-node trees for p <= 8, writes the
+// best rows and folds the chunk's minima into the cluster argmin.  No global scratch, no dependent
+// global loads after the staging, one launch per scheduling cycle.
+constexpr int kChunk = 128;
+
+struct PrioParams {
+    const uint8_t *cost;
+    const uint8_t *n_gpus;
+    const uint16_t *free_mask;
+    uint32_t *best;
+    unsigned long long *place;        // [2][16]: this launch folds into place[parity], resets place[parity^1]
+    uint32_t *ticket;                 // [2]: chunk ticket of this launch = ticket[parity], resets the other
+    uint32_t n_nodes, first_node, parity;
+};
+
+template <int P>
+__device__ __forceinline__ void score_small_tile(const uint8_t *tile, uint32_t f, uint32_t (&out)[16])
+{
+    if constexpr (P > 0) {
+        uint32_t pos[P], bit[P];
+#pragma unroll
+        for (int a = 0; a < P; a++) {
+            const int g = __ffs(f) - 1;
+            f &= f - 1;
+            pos[a] = (uint32_t)g;
+            bit[a] = 1u << g;
+        }
+        uint32_t c[P * P];
+#pragma unroll
+        for (int a = 0; a < P; a++)
+#pragma unroll
+            for (int b = 0; b < P; b++)
+                c[a * P + b] = (a < b) ? ((uint32_t)tile[pos[a] * 16 + pos[b]] << 16) : 0u;
+        uint32_t acc[P + 1], R[P];
+#pragma unroll
+        for (int k = 0; k <= P; k++) acc[k] = kInf;
+#pragma unroll
+        for (int a = 0; a < P; a++) R[a] = 0u;
+        Children<P, P, 0>::run(0u, R, c, bit, acc);
+#pragma unroll
+        for (int k = 1; k <= P; k++) out[k - 1] = acc[k];
+    }
+}
+
+__global__ void __launch_bounds__(kChunk, 4) k_prioritize(PrioParams prm)
+{
+    __shared__ __align__(16) uint8_t s_tile[kChunk * kTileStride];
+    __shared__ uint32_t s_best[kChunk][kBins];        // rows of the chunk's big nodes, by sorted slot
+    __shared__ unsigned long long s_place[16];
+    __shared__ uint32_t s_hist[kBins], s_base[kBins]; // nodes per p; first sorted slot of bin p
+    __shared__ uint32_t s_lane0[kBins];               // first big lane of bin p (p > 8)
+    __shared__ uint32_t s_chunk, s_nbig, s_lanes;
+    __shared__ uint16_t s_free[kChunk];
+    __shared__ uint8_t s_p[kChunk], s_order[kChunk];
+
+    const uint32_t tid = threadIdx.x;
+    if (tid < 16) s_place[tid] = ~0ull;
+    if (blockIdx.x == 0) {   // prepare the other parity for the next launch
+        if (tid < 16) prm.place[(prm.parity ^ 1u) * 16 + tid] = ~0ull;
+        if (tid == 16) prm.ticket[prm.parity ^ 1u] = 0u;
+    }
+    const uint32_t n_chunks = (prm.n_nodes + kChunk - 1) / kChunk;
+    for (;;) {
+        __syncthreads();                      // previous chunk fully consumed
+        if (tid == 0) s_chunk = atomicAdd(prm.ticket + prm.parity, 1u);
+        if (tid < kBins) s_hist[tid] = 0u;
+        __syncthreads();
+        const uint32_t chunk = s_chunk;
+        if (chunk >= n_chunks) break;
+        const uint32_t node0 = chunk * kChunk;
+        const uint32_t live = min((uint32_t)kChunk, prm.n_nodes - node0);
+
+        // ---- stage: free masks, p, cost tiles
+        int p = -1;
+        uint32_t binslot = 0;
+        if (tid < live) {
+            uint32_t ng = prm.n_gpus[node0 + tid];
+            ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
+            const uint32_t f = (uint32_t)prm.free_mask[node0 + tid] & ((1u << ng) - 1u);
+            p = __popc(f);
+            s_free[tid] = (uint16_t)f;
+            s_p[tid] = (uint8_t)p;
+            binslot = atomicAdd(&s_hist[p], 1u);
+        }
+        {
+            const uint4 *src = reinterpret_cast<const uint4 *>(prm.cost + (size_t)node0 * 256);
+            uint4 v[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const uint32_t idx = (uint32_t)i * kChunk + tid;       // 16-byte piece within the chunk
+                v[i] = ((idx >> 4) < live) ? __ldg(src + idx) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const uint32_t idx = (uint32_t)i * kChunk + tid;
+                *reinterpret_cast<uint4 *>(s_tile + (idx >> 4) * kTileStride + (idx & 15u) * 16) = v[i];
+            }
+        }
+        __syncthreads();
+        // ---- sort by p descending: slots [0, nbig) are p = 16..9, then p = 8..0
+        if (tid == 0) {
+            uint32_t slot = 0, lanes = 0;
+            for (int q = 16; q >= 0; q--) {
+                s_base[q] = slot;
+                s_lane0[q] = lanes;
+                slot += s_hist[q];
+                if (q > 8) lanes += s_hist[q] << (q - 8);
+                if (q == 9) s_nbig = slot;
+            }
+            s_lanes = lanes;
+        }
+        __syncthreads();
+        if (p >= 0) s_order[s_base[p] + binslot] = (uint8_t)tid;
+        const uint32_t nbig = s_nbig, lanes = s_lanes;
+        for (uint32_t e = tid; e < nbig * kBins; e += kChunk) (&s_best[0][0])[e] = kInf;
+        __syncthreads();
+
+        // ---- big nodes: 2^(p-8) lanes each, packed back to back
+        for (uint32_t id = tid; id < lanes; id += kChunk) {
+            int q = 16;
+            while (q > 9 && id >= s_lane0[q - 1]) q--;      // s_lane0 grows as q falls
+            const uint32_t rel = id - s_lane0[q];
+            const int hb = q - 8;
+            const uint32_t slot = s_base[q] + (rel >> hb);
+            const uint32_t h = rel & ((1u << hb) - 1u);
+            const uint32_t nl = s_order[slot];
+            score_big_lane(s_tile + nl * kTileStride, s_free[nl], hb, h, &s_best[slot][0]);
+        }
+        __syncthreads();
+        for (uint32_t e = tid; e < nbig * 16; e += kChunk) {
+            const uint32_t slot = e >> 4, k = e & 15u;
+            const uint32_t v = s_best[slot][k + 1];
+            const uint32_t node = node0 + s_order[slot];
+            prm.best[(size_t)node * 16 + k] = v;
+            if (v != kInf) {
+                const unsigned long long key = ((unsigned long long)(v >> 16) << 48) |
+                                               ((unsigned long long)(prm.first_node + node) << 16) | (v & 0xFFFFu);
+                atomicMin(&s_place[k], key);
+            }
+        }
+
+        // ---- small nodes: one thread each, p descending so warps are nearly uniform
+        {
+            const uint32_t nsmall = live - nbig;
+            uint32_t out[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) out[k] = kInf;
+            uint32_t nl = 0xFFFFu;
+            if (tid < nsmall) {
+                nl = s_order[nbig + tid];
+                const uint8_t *tile = s_tile + nl * kTileStride;
+                const uint32_t f = s_free[nl];
+                switch (s_p[nl]) {
+                case 1: score_small_tile<1>(tile, f, out); break;
+                case 2: score_small_tile<2>(tile, f, out); break;
+                case 3: score_small_tile<3>(tile, f, out); break;
+                case 4: score_small_tile<4>(tile, f, out); break;
+                case 5: score_small_tile<5>(tile, f, out); break;
+                case 6: score_small_tile<6>(tile, f, out); break;
+                case 7: score_small_tile<7>(tile, f, out); break;
+                case 8: score_small_tile<8>(tile, f, out); break;
+                default: break;
+                }
+                uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)(node0 + nl) * 16);
+                o[0] = make_uint4(out[0], out[1], out[2], out[3]);
+                o[1] = make_uint4(out[4], out[5], out[6], out[7]);
+                o[2] = make_uint4(kInf, kInf, kInf, kInf);
+                o[3] = make_uint4(kInf, kInf, kInf, kInf);
+            }
+            // chunk minimum per k: lowest cost, then lowest node -> two 32-bit warp reductions
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t cmin = __reduce_min_sync(0xFFFFFFFFu, out[k] & 0xFFFF0000u);
+                if (cmin != kInf) {    // warp-uniform
+                    const uint32_t cand = ((out[k] & 0xFFFF0000u) == cmin) ? nl : 0xFFFFFFFFu;
+                    const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, cand);
+                    if (nl == nmin) {
+                        const unsigned long long key = ((unsigned long long)(cmin >> 16) << 48) |
+                            ((unsigned long long)(prm.first_node + node0 + nl) << 16) | (out[k] & 0xFFFFu);
+                        atomicMin(&s_place[k], key);
+                    }
+                }
+            }
+        }
+    }
+    // the break above happens right after a barrier: s_place is complete for this CTA
+    if (tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + prm.parity * 16 + tid, s_place[tid]);
 }
 
 // ---------------------------------------------------------------- INT32 add peak (roofline denominator)
@@ -355,6 +690,16 @@ __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t ite
     }
     const uint32_t r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
     if (r == 0x12345678u) out[0] = r;
+}
+
+// launch-cadence probes for profiling (no work)
+__global__ void k_noop(uint32_t *out) { if (out == nullptr && threadIdx.x == 9999) out[0] = 0; }
+__global__ void __launch_bounds__(128, 4) k_noop_smem(uint32_t *out)
+{
+    __shared__ uint32_t s[10000];
+    s[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+    if (s[(threadIdx.x + 1) & 127] == 0xFFFFFFFFu) out[0] = 0;
 }
 
 }  // namespace gt

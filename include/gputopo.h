@@ -56,6 +56,8 @@ enum {
 };
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
 enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
+/* GT_FLAG_FUSED_CHUNKS: full passes use the single-launch chunk kernel instead of K0 + K1 (same results) */
+enum { GT_FLAG_FUSED_CHUNKS = 1 };
 
 typedef struct gt_ctx gt_ctx;
 
@@ -65,7 +67,7 @@ typedef struct gt_config {
     uint32_t max_nodes;    /* capacity of this context (its shard of the cluster) */
     uint32_t first_node;   /* global index of local node 0: placement keys carry first_node + local */
     uint32_t k1_policy;    /* GT_K1_*: design.md:154-160 first unused device, or Gaia Alg. 3 */
-    uint32_t flags;        /* reserved, 0 */
+    uint32_t flags;        /* GT_FLAG_* */
     void *stream;          /* optional cudaStream_t to launch on; NULL = the library creates one */
 } gt_config;
 
@@ -124,7 +126,7 @@ uint64_t gt_launch_count(const gt_ctx *ctx);   /* kernels this context has launc
 /* candidate subsets one full scoring pass covers: sum over nodes of 2^popcount(free)-1; optionally
  * the algorithmic pair-cost additions sum C(f,2)*2^(f-2) */
 int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds);
-/* time `iters` back-to-back launches of one kernel ("bin", "score", "argmin", "int32_peak") with
+/* time `iters` back-to-back launches of one kernel ("step", "bin", "score", "argmin", "prioritize", "int32_peak") with
  * CUDA events on the context's stream; out_ms = average per launch */
 int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
 
@@ -135,10 +137,11 @@ int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms
  * fails or fragments the pool), or a latency-critical scheduling loop that cannot afford the
  * device-wide synchronisation cudaMalloc/cudaFree imply.  For them this one call runs K0 + K1
  * (bin by popcount, then score every k-subset) on buffers the CALLER already owns, and keeps the
- * kernels' scratch (bin counters and bin lists, ~272 KiB) in a fixed array inside the library image:
+ * kernels' scratch (bin counters and bin lists, ~408 KiB) in a fixed array inside the library image:
  * every GPU that loads libgputopo.so holds that array until the process exits.
- *   d_cost      n_nodes x 256 u8 pair costs on the device (16x16 per node; with the default cost
- *               table a cost equals the GT_LV_* level code, so level tiles can be passed as they are)
+ *   d_cost      n_nodes x 256 u8 pair costs on the device (16x16 per node, symmetric with a zero
+ *               diagonal; with the default cost table a cost equals the GT_LV_* level code, so the
+ *               level tiles of a symmetric topology matrix can be passed as they are)
  *   d_n_gpus    n_nodes u8, d_free_mask n_nodes u16, d_best n_nodes x 16 u32 (output, as gt_score_all)
  *   stream      cudaStream_t to enqueue on (NULL = the legacy default stream); the call returns
  *               once the work is enqueued -- synchronise the stream before reading d_best

@@ -19,11 +19,17 @@ def all_masks_cluster(oracle, cls):
 
 def check_cluster(gt, oracle, levels, n_gpus, free, lut=None, threads=8):
     lut = oracle.lut(0) if lut is None else lut
+    want, cnt = oracle.exhaustive_cluster(levels, n_gpus, free, lut, threads)
+    # the single-launch chunk kernel must give the same table and placement keys
+    with gt.Allocator(len(n_gpus), flags=gt.FLAG_FUSED_CHUNKS) as a:
+        a.set_cost_lut(lut)
+        a.load_nodes(levels, n_gpus, free)
+        assert (a.score_all() == want).all()
+        assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(want)).all()
     with gt.Allocator(len(n_gpus)) as a:
         a.set_cost_lut(lut)
         a.load_nodes(levels, n_gpus, free)
         got = a.score_all()
-        want, cnt = oracle.exhaustive_cluster(levels, n_gpus, free, lut, threads)
         assert a.count_subsets()[0] == cnt
         bad = np.nonzero((got != want).any(axis=1))[0]
         assert len(bad) == 0, "first mismatch node %d free=%#x got=%s want=%s" % (

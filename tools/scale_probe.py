@@ -1,0 +1,20 @@
+#!/usr/bin/env python
+"""How do the kernels scale with the number of nodes?  (run on the GPU box)"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import _pkg
+
+gt = _pkg.load_package()
+for config in (4, 2, 3):
+    for n in (1000, 10000, 25000, 50000, 100000, 200000, 400000, 800000):
+        if config == 3 and n > 100000:
+            continue
+        lv, ng, fr, _ = gt.synth_cluster(config, 0x5EED0000 + config, 0, n)
+        with gt.Allocator(n) as a:
+            a.load_nodes(lv, ng, fr)
+            subsets, adds = a.count_subsets()
+            t = {k: a.time_kernel(k, 30) * 1e3 for k in ("step", "bin", "score", "prioritize")}
+            print("config %2d N %7d subsets %11d  step %8.2f us  bin %7.2f  score %8.2f  chunks %8.2f   %.3e subsets/s" % (
+                config, n, subsets, t["step"], t["bin"], t["score"], t["prioritize"], subsets / (t["step"] * 1e-6)))
