@@ -257,7 +257,7 @@ def main():
     roofline, kernels = None, {}
     if rank == 0:
         c = ctxs[0]
-        for name in ("step", "bin", "score", "argmin", "prioritize"):
+        for name in ("step", "step_nograph", "bin", "score", "argmin", "prioritize"):
             kernels[name + "_us"] = c.time_kernel(name, 50) * 1e3
         peak_ms = c.time_kernel("int32_peak", 5)
         sms = torch.cuda.get_device_properties(local_rank).multi_processor_count

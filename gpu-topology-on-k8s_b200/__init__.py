@@ -290,3 +290,32 @@ class Allocator:
 def place_fields(key):
     key = int(key)
     return key >> 48, (key >> 16) & 0xFFFFFFFF, key & 0xFFFF
+
+
+def shard_bounds(total_nodes, rank, world):
+    """Contiguous node range of a rank: [rank*N/G, (rank+1)*N/G)."""
+    lo = (total_nodes * rank) // world
+    hi = (total_nodes * (rank + 1)) // world
+    return lo, hi
+
+
+def merge_place(keys_per_shard):
+    """Host-side merge of per-shard placement keys (one process driving several contexts, or ranks
+    exchanging keys over a non-NCCL backend): element-wise minimum of the u64 keys."""
+    out = np.asarray(keys_per_shard[0], np.uint64).copy()
+    for k in keys_per_shard[1:]:
+        out = np.minimum(out, np.asarray(k, np.uint64))
+    return out
+
+
+def allreduce_place_torch(keys, group=None):
+    """Minimum of the placement keys over a torch.distributed group whose backend has no unsigned
+    64-bit type (gloo): GT_NO_PLACE is mapped to INT64_MAX for the exchange."""
+    import torch
+    import torch.distributed as dist
+    k = np.asarray(keys, np.uint64)
+    no = k == np.uint64(NO_PLACE)
+    t = torch.from_numpy(np.where(no, np.uint64(2 ** 63 - 1), k).astype(np.int64))
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    r = t.numpy().astype(np.uint64)
+    return np.where(r == np.uint64(2 ** 63 - 1), np.uint64(NO_PLACE), r)

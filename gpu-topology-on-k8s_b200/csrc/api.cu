@@ -68,10 +68,19 @@ struct gt_ctx {
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
     uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
-    unsigned long long *d_place = nullptr;      // [3][16]: two parities of the fused kernel, [2] = binned path
+    unsigned long long *d_place = nullptr;      // [4][16]: two parities of the chunk kernel, two of the K0+K1 path
     unsigned long long *place_cur = nullptr;    // where the latest placement keys are
     uint32_t *d_ticket = nullptr;               // [2] chunk tickets of the fused kernel
     uint32_t parity = 0;
+    cudaGraphExec_t step_exec[2] = {nullptr, nullptr};   // captured K0 + K1 of a full pass, per place parity
+    uint32_t step_nodes = 0;                    // n_nodes the graphs were captured for
+    bool graph_failed = false;
+    uint32_t bin_parity = 0;                    // placement-key buffer the next pass writes
+    // multi-GPU: the 128-byte min-exchange runs on its own stream so it overlaps the next pass
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t ev_pass = nullptr, ev_comm[2] = {nullptr, nullptr};
+    bool comm_used[2] = {false, false};
+    int comm_last = -1;                         // parity whose exchange is the latest one in flight
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
@@ -172,40 +181,109 @@ void mark_dirty(gt_ctx *c, uint32_t node)
     c->place_valid = false;
 }
 
-gt::ScoreParams score_params(gt_ctx *c, bool fold, bool keep_bins)
+unsigned long long *bin_place(gt_ctx *c, uint32_t parity) { return c->d_place + 32 + 16 * parity; }
+
+gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep_bins)
 {
     gt::ScoreParams p;
     p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
-    p.bin_free = c->d_bin_free; p.place = c->d_place + 32; p.cap = c->cap; p.first_node = c->first_node;
-    p.fold_place = fold ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u;
+    p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
+    p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u;
     return p;
 }
 
 // K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
-int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, bool preset_place)
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place)
 {
     gt::k_bin<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
         c->d_ngpus, c->d_free, d_ids, n, c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best,
-        preset_place ? c->d_place + 32 : nullptr);
+        preset_place);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     return GT_OK;
 }
 
-int launch_score(gt_ctx *c, uint32_t n, bool fold, bool keep_bins = false)
+int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins = false)
 {
     // persistent warps: every resident CTA slot, fewer when there is little work
     const uint32_t grid = std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::kScoreMinCtas);
-    gt::k_score<<<grid, gt::kScoreCta, 0, c->stream>>>(score_params(c, fold, keep_bins));
+    // programmatic dependent launch: K1's CTAs are scheduled while K0 drains and wait inside the kernel
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(gt::kScoreCta);
+    cfg.stream = c->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, score_params(c, fold, keep_bins)));
     c->launches++;
-    GT_CUDA(c, cudaGetLastError());
-    if (fold) c->place_cur = c->d_place + 32;
+    if (fold) c->place_cur = fold;
+    return GT_OK;
+}
+
+// Multi-GPU: min of the 16 placement keys over all ranks, on the communication stream.  The pass that
+// produced `place` is ordered before it by an event; consumers wait for ev_comm[parity].
+int nccl_min(gt_ctx *c, unsigned long long *place, uint32_t parity)
+{
+    if (!c->comm) return GT_OK;
+    NcclApi *api = nccl_api();
+    GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
+    GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
+    int e = api->AllReduce(place, place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    GT_CUDA(c, cudaEventRecord(c->ev_comm[parity], c->comm_stream));
+    c->comm_used[parity] = true;
+    c->comm_last = (int)parity;
+    return GT_OK;
+}
+
+// before a pass overwrites place[parity]: the exchange that last used that buffer must be finished
+int wait_place_free(gt_ctx *c, uint32_t parity)
+{
+    if (c->comm && c->comm_used[parity]) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[parity], 0));
+    return GT_OK;
+}
+
+// full pass as one graph launch: K0 -> K1, captured once per node count and place parity
+int launch_step_graph(gt_ctx *c, uint32_t parity)
+{
+    if (c->step_nodes != c->n_nodes) {
+        for (auto &g : c->step_exec)
+            if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+    }
+    if (!c->step_exec[parity]) {
+        cudaGraph_t graph = nullptr;
+        const uint64_t before = c->launches;
+        GT_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, parity));
+        if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, parity));
+        cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        c->launches = before;
+        if (rc != GT_OK || e != cudaSuccess || !graph) {
+            cudaGetLastError();
+            if (graph) cudaGraphDestroy(graph);
+            return GT_ERR_CUDA;
+        }
+        e = cudaGraphInstantiate(&c->step_exec[parity], graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            c->step_exec[parity] = nullptr;
+            return GT_ERR_CUDA;
+        }
+        c->step_nodes = c->n_nodes;
+    }
+    GT_CUDA(c, cudaGraphLaunch(c->step_exec[parity], c->stream));
+    c->launches += 2;
+    c->place_cur = bin_place(c, parity);
     return GT_OK;
 }
 
 int launch_argmin(gt_ctx *c)
 {
-    unsigned long long *place = c->d_place + 32;
+    unsigned long long *place = bin_place(c, c->bin_parity);
     GT_CUDA(c, cudaMemsetAsync(place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
     const size_t quarters = (size_t)c->n_nodes * 4;      // 16-byte pieces; 8 per thread
     const uint32_t grid = (uint32_t)std::min<size_t>((quarters + gt::kCta * 8 - 1) / (gt::kCta * 8), (size_t)c->num_sms * 4);
@@ -239,25 +317,38 @@ int launch_prioritize(gt_ctx *c)
 int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
     int rc;
+    const uint32_t par = c->bin_parity;
+    if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
     if (!d_ids && n) {
         if (c->flags & GT_FLAG_FUSED_CHUNKS) {
             if ((rc = launch_prioritize(c)) != GT_OK) return rc;
-        } else {
-            if ((rc = launch_bin(c, nullptr, n, true)) != GT_OK) return rc;
-            if ((rc = launch_score(c, n, true)) != GT_OK) return rc;
+            if (c->comm) {   // the chunk kernel reuses its two buffers every other launch: exchange in stream order
+                NcclApi *api = nccl_api();
+                int e = api->AllReduce(c->place_cur, c->place_cur, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
+                if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce failed%s");
+                c->comm_last = -1;
+            }
+            c->best_valid = c->place_valid = true;
+            return GT_OK;
+        }
+        bool done = false;
+        if (!(c->flags & GT_FLAG_NO_GRAPH) && !c->graph_failed) {
+            done = launch_step_graph(c, par) == GT_OK;
+            if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
+        }
+        if (!done) {
+            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, bin_place(c, par))) != GT_OK) return rc;
         }
     } else {
         if (n) {
-            if ((rc = launch_bin(c, d_ids, n, false)) != GT_OK) return rc;
-            if ((rc = launch_score(c, n, false)) != GT_OK) return rc;
+            if ((rc = launch_bin(c, d_ids, n, nullptr)) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, nullptr)) != GT_OK) return rc;
         }
         if ((rc = launch_argmin(c)) != GT_OK) return rc;
     }
-    if (c->comm) {
-        NcclApi *api = nccl_api();
-        int e = api->AllReduce(c->place_cur, c->place_cur, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
-        if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
-    }
+    if ((rc = nccl_min(c, c->place_cur, par)) != GT_OK) return rc;
+    c->bin_parity ^= 1u;
     c->best_valid = true;
     c->place_valid = true;
     return GT_OK;
@@ -327,8 +418,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_free, (size_t)gt::kBins * N * sizeof(uint16_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMalloc(&c->d_place, 48 * sizeof(unsigned long long)));
-        GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 48 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMalloc(&c->d_place, 64 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 64 * sizeof(unsigned long long)));
         GT_CUDA(c, cudaMalloc(&c->d_ticket, 2 * sizeof(uint32_t)));
         GT_CUDA(c, cudaMemset(c->d_ticket, 0, 2 * sizeof(uint32_t)));
         c->place_cur = c->d_place + 32;
@@ -375,6 +466,12 @@ void gt_destroy(gt_ctx *c)
     cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_ticket);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
+    for (auto &g : c->step_exec)
+        if (g) cudaGraphExecDestroy(g);
+    if (c->comm_stream) { cudaStreamSynchronize(c->comm_stream); cudaStreamDestroy(c->comm_stream); }
+    if (c->ev_pass) cudaEventDestroy(c->ev_pass);
+    for (auto &e : c->ev_comm)
+        if (e) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -482,6 +579,7 @@ int gt_sync(gt_ctx *c)
     if (!c) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     return GT_OK;
 }
 
@@ -520,6 +618,7 @@ int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place
         int rc = enqueue_scoring(c, nullptr, 0);
         if (rc != GT_OK) return rc;
     }
+    if (c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
     GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
     for (uint32_t i = 0; i < nreq; i++)
@@ -566,6 +665,12 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
 {
     if (!c || !which || !out_ms || !iters) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
+    // a local measurement: no collective may be issued from here (other ranks are not in this call)
+    struct CommOff {
+        gt_ctx *c; void *saved;
+        explicit CommOff(gt_ctx *x) : c(x), saved(x->comm) { x->comm = nullptr; }
+        ~CommOff() { c->comm = saved; c->place_valid = false; }
+    } comm_off(c);
     int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
     if (rc != GT_OK) return rc;
     clear_dirty(c);
@@ -577,12 +682,16 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     auto one = [&]() -> int {
         if (w == "bin") {   // K0 alone: its counters have to be cleared by hand between launches
             GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
-            return launch_bin(c, nullptr, c->n_nodes, true);
+            return launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
         }
-        if (w == "score") return launch_score(c, c->n_nodes, true, true);
+        if (w == "score") return launch_score(c, c->n_nodes, bin_place(c, 0), true);
         if (w == "argmin") return launch_argmin(c);
         if (w == "prioritize") return launch_prioritize(c);
         if (w == "step") return enqueue_scoring(c, nullptr, c->n_nodes);
+        if (w == "step_nograph") {
+            int r2 = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
+            return r2 != GT_OK ? r2 : launch_score(c, c->n_nodes, bin_place(c, 0));
+        }
         if (w == "noop") { gt::k_noop<<<1, 32, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
         if (w == "noop_grid") { gt::k_noop<<<c->num_sms * 4, 128, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
         if (w == "noop_smem") { gt::k_noop_smem<<<c->num_sms * 4, 128, 0, c->stream>>>(c->d_peak_out); return GT_OK; }
@@ -594,8 +703,8 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
         return GT_ERR_INVALID;
     };
     if (w == "score" || w == "argmin") {   // bins / best table must exist
-        if ((rc = launch_bin(c, nullptr, c->n_nodes, true)) != GT_OK) return rc;
-        if ((rc = launch_score(c, c->n_nodes, true, true)) != GT_OK) return rc;
+        if ((rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0))) != GT_OK) return rc;
+        if ((rc = launch_score(c, c->n_nodes, bin_place(c, 0), true)) != GT_OK) return rc;
     }
     if ((rc = one()) != GT_OK) return rc;   // warm-up
     GT_CUDA(c, cudaEventRecord(e0, c->stream));
@@ -640,6 +749,14 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     }
     c->rank = rank;
     c->world = world;
+    GT_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_pass, cudaEventDisableTiming));
+    for (auto &ev : c->ev_comm) GT_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    // one exchange now, so connections are set up before any timed or latency-critical pass
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    e = api->AllReduce(c->d_place, c->d_place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce (warm-up): %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     c->place_valid = false;
     return GT_OK;
 }

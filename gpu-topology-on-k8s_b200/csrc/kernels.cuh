@@ -28,7 +28,7 @@ constexpr int kCta = 256;
 constexpr uint32_t kInf = 0xFFFF0000u;
 constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
 #ifndef GT_SCORE_MIN_CTAS
-#define GT_SCORE_MIN_CTAS 4
+#define GT_SCORE_MIN_CTAS 5
 #endif
 constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the register budget is set for
 constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
@@ -89,6 +89,9 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
+    // programmatic dependent launch: K1 may be scheduled now; it waits (griddepcontrol.wait) for this
+    // grid to complete before it reads the bins
+    asm volatile("griddepcontrol.launch_dependents;");
     if (tid < kBins) s_cnt[tid] = 0;
     if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     __syncthreads();
@@ -346,6 +349,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     __shared__ uint32_t s_cnt[kBins], s_end[kBins];   // s_end[i]: cumulative units after bin p = 16 - i
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     if (tid < 16) s_place[tid] = ~0ull;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible (no-op without PDL)
     if (tid < kBins) s_cnt[tid] = prm.ctl[tid];
     __syncthreads();
     if (tid == 0) {
@@ -366,13 +370,13 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // (plain PTX atom: the compiler's warp-aggregated atomicAdd would wait for the reply right away)
     const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
     uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
+    int i = 0;
     while (u < total) {
         uint32_t next = 0;
         if (lane == 0)
             asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket) : "memory");
         next += n_warps;
-        int i = 0;
-        while (u >= s_end[i]) i++;
+        while (u >= s_end[i]) i++;            // units only grow: continue from the previous bin
         const int p = 16 - i;
         const uint32_t lu = u - (i ? s_end[i - 1] : 0u);
         const uint32_t cnt = s_cnt[p];

@@ -57,7 +57,7 @@ enum {
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
 enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
 /* GT_FLAG_FUSED_CHUNKS: full passes use the single-launch chunk kernel instead of K0 + K1 (same results) */
-enum { GT_FLAG_FUSED_CHUNKS = 1 };
+enum { GT_FLAG_FUSED_CHUNKS = 1, GT_FLAG_NO_GRAPH = 2 /* launch K0, K1 one by one instead of as a CUDA graph */ };
 
 typedef struct gt_ctx gt_ctx;
 

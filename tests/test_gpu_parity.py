@@ -189,3 +189,21 @@ def test_full_size_properties(gt, oracle):
         assert (best[idx] == want).all()
         # the cluster argmin is a checksum over the whole table
         assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(best)).all()
+
+
+def test_sharded_contexts_agree_with_one_context(gt, oracle):
+    """Node sharding invariance on one GPU: 1, 2 and 4 contexts with global node
+    offsets, keys merged with min, must name the same winners (global node index is inside the key)."""
+    total = 40000
+    lv, n, fr, _ = gt.synth_cluster(4, 0x5EED0004, 0, total)
+    ks = np.arange(1, 17, dtype=np.uint8)
+    want = oracle.cluster_argmin(oracle.exhaustive_cluster(lv, n, fr, oracle.lut(0), 8)[0])
+    for world in (1, 2, 4):
+        keys = []
+        for r in range(world):
+            lo, hi = gt.shard_bounds(total, r, world)
+            with gt.Allocator(hi - lo, first_node=lo) as a:
+                a.load_nodes(lv[lo:hi], n[lo:hi], fr[lo:hi])
+                a.score_all(fetch=False)
+                keys.append(a.best_node(ks))
+        assert (gt.merge_place(keys) == want).all()

@@ -7,8 +7,13 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import _pkg
 
 gt = _pkg.load_package()
-for config in (4, 2, 3):
-    for n in (1000, 10000, 25000, 50000, 100000, 200000, 400000, 800000):
+configs = (4, 2, 3)
+sizes = (1000, 10000, 25000, 50000, 100000, 200000, 400000, 800000)
+if len(sys.argv) > 1:
+    configs = (int(sys.argv[1]),)
+    sizes = tuple(int(x) for x in sys.argv[2:]) or sizes
+for config in configs:
+    for n in sizes:
         if config == 3 and n > 100000:
             continue
         lv, ng, fr, _ = gt.synth_cluster(config, 0x5EED0000 + config, 0, n)
