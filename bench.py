@@ -297,6 +297,31 @@ def main():
                         "sample": "first %d nodes of the config-4 cluster (%d subsets), oracle/gt_oracle.c -O2" % (sample, cnt),
                         "all_cores": {"value": cntm / dtm, "cores": cores}}
 
+    placements = None
+    if rank == 0 and world == 1:
+        # pod placements/s: BASELINE config 5 (1M-event arrival/departure trace) on the config-2 cluster, through
+        # gt_schedule (GPU-built memo table + host commit loop, sequential semantics)
+        lv2, n2, fr2, _ = gt.synth_cluster(2, 0x5EED0002, 0, 1000)
+        ek, ea = gt.synth_events(5, 0x5EED0005, 1000000)
+        with gt.Allocator(1000, device=local_rank) as a:
+            a.load_nodes(lv2, n2, fr2)
+            a.schedule(ek[:1000], ea[:1000])          # warm-up: builds the memo table on the GPU
+            a.update_free(fr2)
+            t0 = time.perf_counter()
+            placed, _, _ = a.schedule(ek, ea)
+            dt = time.perf_counter() - t0
+        placements = {"value": placed / dt, "unit": "placements/s", "events": len(ek), "events_per_s": len(ek) / dt,
+                      "placed": placed, "seconds": dt,
+                      "workload": "config5: 1M arrival/departure events on 1000 DGX-1 nodes (config 2 cluster), sequential"}
+        if not args.no_cpu_baseline:
+            oracle = load_oracle()
+            sub = 100000
+            t0 = time.perf_counter()
+            op, _, _, _ = oracle.replay(lv2, n2, fr2, oracle.lut(0), ek[:sub], ea[:sub])
+            odt = time.perf_counter() - t0
+            placements["cpu_baseline"] = {"value": op / odt, "unit": "placements/s", "cores": 1, "kind": "port",
+                                          "sample": "first %d events of the same trace, oracle gto_replay" % sub}
+
     if rank == 0:
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -306,7 +331,7 @@ def main():
                        "subsets_per_step_per_gpu": subsets[0], "parallelism": "nodes sharded, %d rank(s)" % world,
                        "l2": "%d cluster replicas rotated between steps (%.0f MB of tables > 126 MB L2)" % (R, read_mb)},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernels_us": kernels,
-            "cpu_baseline": cpu_baseline,
+            "cpu_baseline": cpu_baseline, "placements": placements,
         }))
     for c in ctxs:
         c.close()

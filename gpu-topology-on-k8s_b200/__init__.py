@@ -18,14 +18,14 @@ NO_PLACE = 0xFFFFFFFFFFFFFFFF
 LV = dict(X=0, NVS=1, NV4=2, NV3=3, NV2=4, NV1=5, PSB=6, PIX=7, PXB=8, PHB=9, NODE=10, SYS=11)
 LUT_DEFAULT, LUT_DESIGN_MARKS = 0, 1
 K1_FIRST_UNUSED, K1_GAIA_SINGULAR = 0, 1
-FLAG_FUSED_CHUNKS = 1
+FLAG_FUSED_CHUNKS, FLAG_NO_GRAPH, FLAG_NO_MEMO = 1, 2, 4
 
 EXPORTS = [
     "gt_create", "gt_destroy", "gt_strerror", "gt_last_error", "gt_lut_preset", "gt_set_cost_lut",
     "gt_score_int", "gt_score_milli", "gt_load_nodes", "gt_update_free", "gt_score_all", "gt_score_dirty",
     "gt_best_node", "gt_allocate", "gt_commit", "gt_release", "gt_score_all_async", "gt_sync", "gt_stream",
     "gt_device_best", "gt_num_nodes", "gt_launch_count", "gt_count_subsets", "gt_time_kernel",
-    "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static",
+    "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static", "gt_schedule", "gt_synth_events",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -97,6 +97,8 @@ def _lib():
     L.gt_comm_unique_id.argtypes = [u8p]
     L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
+    L.gt_schedule.argtypes = [C.c_void_p, u8p, u32p, C.c_uint32, u32p, u16p, u64p]
+    L.gt_synth_events.argtypes = [C.c_int, C.c_uint64, C.c_uint32, u8p, u32p]
     L.gt_score_nodes_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
                                         C.c_char_p, C.c_size_t]
     _LIB = L
@@ -146,6 +148,15 @@ def score_nodes_static(d_cost, d_n_gpus, d_free_mask, n_nodes, d_best, stream=No
     rc = _lib().gt_score_nodes_static(d_cost, d_n_gpus, d_free_mask, n_nodes, d_best, stream, buf, len(buf))
     if rc:
         raise GtError(rc, "gt_score_nodes_static", buf.value.decode())
+
+
+def synth_events(config, seed, n_events):
+    k = np.zeros(n_events, np.uint8)
+    arg = np.zeros(n_events, np.uint32)
+    rc = _lib().gt_synth_events(config, seed, n_events, _p(k, u8p), _p(arg, u32p))
+    if rc:
+        raise GtError(rc, "gt_synth_events")
+    return k, arg
 
 
 def comm_unique_id():
@@ -270,6 +281,18 @@ class Allocator:
         nodes = np.ascontiguousarray(nodes, np.uint32)
         masks = np.ascontiguousarray(masks, np.uint16)
         self._ck(self._L.gt_release(self._h, _p(nodes, u32p), _p(masks, u16p), len(nodes)), "gt_release")
+
+    def schedule(self, ev_k, ev_arg):
+        """Sequential sort -> bind loop over an event trace.  Returns (placed, node[], mask[])."""
+        ev_k = np.ascontiguousarray(ev_k, np.uint8)
+        ev_arg = np.ascontiguousarray(ev_arg, np.uint32)
+        n = len(ev_k)
+        on = np.zeros(n, np.uint32)
+        om = np.zeros(n, np.uint16)
+        placed = C.c_uint64(0)
+        self._ck(self._L.gt_schedule(self._h, _p(ev_k, u8p), _p(ev_arg, u32p), n, _p(on, u32p), _p(om, u16p),
+                                     C.byref(placed)), "gt_schedule")
+        return int(placed.value), on, om
 
     def count_subsets(self):
         s = C.c_uint64(0)

@@ -11,6 +11,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace {
@@ -98,6 +99,14 @@ struct gt_ctx {
     uint64_t launches = 0;
     void *comm = nullptr;
     int rank = 0, world = 1;
+    // commit loop (gt_schedule): topology classes seen by gt_load_nodes and the memo table the GPU fills
+    std::unordered_map<std::string, uint32_t> class_of_tile;   // 256 level bytes + n_gpus -> class id
+    std::vector<std::string> class_tile;
+    std::vector<uint32_t> node_class;
+    std::vector<uint32_t> memo;            // [sum over classes of 2^n][16] best rows, filled by K0+K1
+    std::vector<size_t> memo_off;          // first row of each class
+    uint32_t memo_classes = 0;             // classes covered by `memo`
+    uint64_t lut_version = 0, memo_lut_version = ~0ull;
     char err[256];
 };
 
@@ -441,6 +450,7 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         memset(c->h_free, 0, N * 2);
         memset(c->h_ngpus, 0, N);
         c->dirty_flag.assign(N, 0);
+        c->node_class.assign(N, 0);
         return GT_OK;
     }();
     if (rc != GT_OK) {
@@ -481,6 +491,7 @@ int gt_set_cost_lut(gt_ctx *c, const uint8_t lut[16])
     if (!c || !lut) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
     memcpy(c->lut, lut, 16);
+    c->lut_version++;
     c->best_valid = c->place_valid = false;
     int rc = apply_lut(c, 0, c->n_nodes);
     if (rc != GT_OK) return rc;
@@ -500,6 +511,19 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
     GT_CUDA(c, cudaMemcpyAsync(c->d_levels + (size_t)first * 256, levels, (size_t)count * 256, cudaMemcpyHostToDevice, c->stream));
     memcpy(c->h_ngpus + first, n_gpus, count);
     memcpy(c->h_free + first, free_mask, (size_t)count * 2);
+    {   // topology classes: nodes with the same level matrix and GPU count share one memo table
+        std::string key(257, '\0');
+        for (uint32_t i = 0; i < count; i++) {
+            memcpy(&key[0], levels + (size_t)i * 256, 256);
+            key[256] = (char)n_gpus[i];
+            auto it = c->class_of_tile.find(key);
+            if (it == c->class_of_tile.end()) {
+                it = c->class_of_tile.emplace(key, (uint32_t)c->class_tile.size()).first;
+                c->class_tile.push_back(key);
+            }
+            c->node_class[first + i] = it->second;
+        }
+    }
     GT_CUDA(c, cudaMemcpyAsync(c->d_ngpus + first, c->h_ngpus + first, count, cudaMemcpyHostToDevice, c->stream));
     GT_CUDA(c, cudaMemcpyAsync(c->d_free + first, c->h_free + first, (size_t)count * 2, cudaMemcpyHostToDevice, c->stream));
     if (access_cost)
@@ -758,6 +782,204 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce (warm-up): %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     c->place_valid = false;
+    return GT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// gt_schedule: the sequential sort -> bind loop, one event at a time.
+namespace {
+
+constexpr size_t kMemoMaxBytes = (size_t)1 << 30;
+
+// GPU fills best rows for every free mask of every topology class (3^n subsets per class)
+int build_memo(gt_ctx *c)
+{
+    const uint32_t ncls = (uint32_t)c->class_tile.size();
+    if (c->memo_classes == ncls && c->memo_lut_version == c->lut_version) return GT_OK;
+    size_t rows = 0;
+    c->memo_off.assign(ncls, 0);
+    for (uint32_t k = 0; k < ncls; k++) {
+        c->memo_off[k] = rows;
+        rows += (size_t)1 << (uint8_t)c->class_tile[k][256];
+    }
+    if (rows * 64 > kMemoMaxBytes || rows > 0x7FFFFFFFull) return GT_ERR_RANGE;
+    gt_config cfg = {};
+    cfg.struct_size = sizeof cfg;
+    cfg.device = c->device;
+    cfg.max_nodes = (uint32_t)rows;
+    gt_ctx *m = nullptr;
+    int rc = gt_create(&cfg, &m);
+    if (rc != GT_OK) return fail(c, rc, "gt_schedule: memo context: %s", gt_strerror(rc));
+    rc = gt_set_cost_lut(m, c->lut);
+    std::vector<uint8_t> lv, ng;
+    std::vector<uint16_t> fr;
+    const size_t batch = (size_t)1 << 16;
+    for (uint32_t k = 0; k < ncls && rc == GT_OK; k++) {
+        const uint32_t n = (uint8_t)c->class_tile[k][256];
+        const size_t cnt = (size_t)1 << n;
+        for (size_t b0 = 0; b0 < cnt && rc == GT_OK; b0 += batch) {
+            const size_t bn = std::min(batch, cnt - b0);
+            lv.resize(bn * 256); ng.assign(bn, (uint8_t)n); fr.resize(bn);
+            for (size_t i = 0; i < bn; i++) {
+                memcpy(&lv[i * 256], c->class_tile[k].data(), 256);
+                fr[i] = (uint16_t)(b0 + i);
+            }
+            rc = gt_load_nodes(m, (uint32_t)(c->memo_off[k] + b0), (uint32_t)bn, lv.data(), ng.data(), nullptr, nullptr,
+                               fr.data());
+        }
+    }
+    if (rc == GT_OK) {
+        c->memo.resize(rows * 16);
+        rc = gt_score_all(m, c->memo.data());
+    }
+    if (rc != GT_OK) fail(c, rc, "gt_schedule: memo build: %s", gt_last_error(m));
+    c->launches += gt_launch_count(m);
+    gt_destroy(m);
+    if (rc != GT_OK) return rc;
+    c->memo_classes = ncls;
+    c->memo_lut_version = c->lut_version;
+    return GT_OK;
+}
+
+// per-k tournament tree over the nodes' placement keys
+struct MinTree {
+    uint32_t leaves = 1;
+    std::vector<unsigned long long> t[16];
+    void init(uint32_t n)
+    {
+        leaves = 1;
+        while (leaves < n) leaves <<= 1;
+        for (auto &v : t) v.assign((size_t)2 * leaves, ~0ull);
+    }
+    void build()
+    {
+        for (auto &v : t)
+            for (uint32_t i = leaves - 1; i >= 1; i--) v[i] = std::min(v[2 * i], v[2 * i + 1]);
+    }
+    void set(int k, uint32_t node, unsigned long long key)
+    {
+        auto &v = t[k];
+        uint32_t i = leaves + node;
+        v[i] = key;
+        for (i >>= 1; i >= 1; i >>= 1) {
+            const unsigned long long m = std::min(v[2 * i], v[2 * i + 1]);
+            if (v[i] == m) break;
+            v[i] = m;
+        }
+    }
+};
+
+inline unsigned long long place_key(uint32_t b, uint32_t global_node)
+{
+    return b == GT_INFEASIBLE ? ~0ull
+                              : ((unsigned long long)(b >> 16) << 48) | ((unsigned long long)global_node << 16) | (b & 0xFFFFu);
+}
+
+}  // namespace
+
+int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
+                uint16_t *out_mask, uint64_t *out_placed)
+{
+    if (!c || (n_events && (!ev_k || !ev_arg || !out_node || !out_mask))) return GT_ERR_INVALID;
+    if (c->comm) return fail(c, GT_ERR_STATE, "gt_schedule: not available on a sharded (multi-rank) context%s");
+    GT_CUDA(c, cudaSetDevice(c->device));
+    uint64_t placed = 0;
+    std::vector<uint32_t> live_node;
+    std::vector<uint16_t> live_mask;
+    int rc = (c->flags & GT_FLAG_NO_MEMO) ? GT_ERR_RANGE : build_memo(c);
+    if (rc != GT_OK && rc != GT_ERR_RANGE) return rc;
+    if (rc == GT_ERR_RANGE) {
+        // too many distinct topologies for a memo table: every event re-scores the touched node on the GPU
+        if ((rc = gt_score_dirty(c)) != GT_OK) return rc;
+        for (uint32_t e = 0; e < n_events; e++) {
+            out_node[e] = 0xFFFFFFFFu; out_mask[e] = 0;
+            if (ev_k[e] == 0) {
+                if (live_node.empty()) continue;
+                const size_t idx = ev_arg[e] % live_node.size();
+                const uint32_t nd = live_node[idx]; const uint16_t m = live_mask[idx];
+                if ((rc = gt_release(c, &nd, &m, 1)) != GT_OK) return rc;
+                out_node[e] = c->first_node + nd; out_mask[e] = m;
+                live_node[idx] = live_node.back(); live_node.pop_back();
+                live_mask[idx] = live_mask.back(); live_mask.pop_back();
+            } else {
+                uint64_t key;
+                const uint8_t k = ev_k[e];
+                if ((rc = gt_best_node(c, &k, 1, &key)) != GT_OK) return rc;
+                if (key == GT_NO_PLACE) continue;
+                const uint32_t nd = GT_PLACE_NODE(key) - c->first_node; const uint16_t m = (uint16_t)GT_PLACE_MASK(key);
+                if ((rc = gt_commit(c, &nd, &m, 1)) != GT_OK) return rc;
+                out_node[e] = c->first_node + nd; out_mask[e] = m;
+                live_node.push_back(nd); live_mask.push_back(m);
+                placed++;
+            }
+            if ((rc = gt_score_dirty(c)) != GT_OK) return rc;
+        }
+        if (out_placed) *out_placed = placed;
+        return GT_OK;
+    }
+    // memo path: the GPU has scored every (class, free mask); the host loop only looks rows up
+    const uint32_t N = c->n_nodes;
+    MinTree tree;
+    tree.init(std::max(N, 1u));
+    auto row_of = [&](uint32_t nd) -> const uint32_t * {
+        const uint32_t cls = c->node_class[nd];
+        const uint32_t n = c->h_ngpus[nd];
+        const uint32_t f = c->h_free[nd] & ((1u << n) - 1u);
+        return &c->memo[(c->memo_off[cls] + f) * 16];
+    };
+    for (uint32_t nd = 0; nd < N; nd++) {
+        const uint32_t *row = row_of(nd);
+        for (int k = 0; k < 16; k++) tree.t[k][tree.leaves + nd] = place_key(row[k], c->first_node + nd);
+    }
+    tree.build();
+    auto refresh = [&](uint32_t nd) {
+        const uint32_t *row = row_of(nd);
+        for (int k = 0; k < 16; k++) tree.set(k, nd, place_key(row[k], c->first_node + nd));
+        mark_dirty(c, nd);
+    };
+    for (uint32_t e = 0; e < n_events; e++) {
+        out_node[e] = 0xFFFFFFFFu; out_mask[e] = 0;
+        if (ev_k[e] == 0) {
+            if (live_node.empty()) continue;
+            const size_t idx = ev_arg[e] % live_node.size();
+            const uint32_t nd = live_node[idx]; const uint16_t m = live_mask[idx];
+            c->h_free[nd] |= m;
+            out_node[e] = c->first_node + nd; out_mask[e] = m;
+            live_node[idx] = live_node.back(); live_node.pop_back();
+            live_mask[idx] = live_mask.back(); live_mask.pop_back();
+            refresh(nd);
+        } else if (ev_k[e] <= 16) {
+            const unsigned long long key = tree.t[ev_k[e] - 1][1];
+            if (key == ~0ull) continue;
+            const uint32_t nd = GT_PLACE_NODE(key) - c->first_node; const uint16_t m = (uint16_t)GT_PLACE_MASK(key);
+            c->h_free[nd] &= (uint16_t)~m;
+            out_node[e] = c->first_node + nd; out_mask[e] = m;
+            live_node.push_back(nd); live_mask.push_back(m);
+            placed++;
+            refresh(nd);
+        }
+    }
+    if (out_placed) *out_placed = placed;
+    return GT_OK;
+}
+
+int gt_synth_events(int config, uint64_t seed, uint32_t n_events, uint8_t *ev_k, uint32_t *ev_arg)
+{
+    if (!ev_k || !ev_arg || (config != 2 && config != 5)) return GT_ERR_INVALID;
+    auto sm = [&](uint64_t index) {
+        uint64_t z = seed + (index + 1) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    };
+    for (uint32_t i = 0; i < n_events; i++) {
+        const uint64_t a = sm(2ull * i), b = sm(2ull * i + 1);
+        if (config == 5 && (uint32_t)(a >> 32) >= 2362232012u) {   // floor(0.55 * 2^32): arrival below, departure above
+            ev_k[i] = 0; ev_arg[i] = (uint32_t)(b >> 32);
+        } else {
+            ev_k[i] = (uint8_t)(1 + b % 8u); ev_arg[i] = 0;
+        }
+    }
     return GT_OK;
 }
 

@@ -57,7 +57,8 @@ enum {
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
 enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
 /* GT_FLAG_FUSED_CHUNKS: full passes use the single-launch chunk kernel instead of K0 + K1 (same results) */
-enum { GT_FLAG_FUSED_CHUNKS = 1, GT_FLAG_NO_GRAPH = 2 /* launch K0, K1 one by one instead of as a CUDA graph */ };
+enum { GT_FLAG_FUSED_CHUNKS = 1, GT_FLAG_NO_GRAPH = 2 /* launch K0, K1 one by one instead of as a CUDA graph */,
+       GT_FLAG_NO_MEMO = 4 /* gt_schedule re-scores on the GPU per event instead of using the memo table */ };
 
 typedef struct gt_ctx gt_ctx;
 
@@ -116,6 +117,17 @@ int gt_allocate(gt_ctx *ctx, uint32_t node, uint32_t k, uint16_t *out_mask, uint
 int gt_commit(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32_t count);
 int gt_release(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32_t count);
 
+/* replaces: the scheduling cycle itself -- kube-scheduler handing pods one at a time to "sort" then
+ * "bind" (design.md:115-119), each pod seeing the previous pod's effect.  Events: ev_k[i] > 0 = a pod
+ * asking for ev_k[i] GPUs (placed on the best node, lowest cost then lowest index, and committed);
+ * ev_k[i] == 0 = the live pod number (ev_arg[i] % live pods) leaves and its GPUs are released.
+ * out_node / out_mask per event (0xFFFFFFFF / 0 when unplaceable or nothing to release).
+ * The GPU scores every (topology class, free mask) once (3^n subsets per class) into a memo table and
+ * the host commit loop looks rows up; with too many distinct topologies for that table (> 1 GiB), or
+ * GT_FLAG_NO_MEMO, the touched node is re-scored on the GPU after every event.  No CPU scoring. */
+int gt_schedule(gt_ctx *ctx, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
+                uint16_t *out_mask, uint64_t *out_placed);
+
 /* ---- asynchronous / measurement surface ---- */
 int gt_score_all_async(gt_ctx *ctx);     /* enqueue scoring + cluster argmin, no copies, no sync */
 int gt_sync(gt_ctx *ctx);
@@ -165,6 +177,8 @@ int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
 int gt_synth_cluster(int config, uint64_t seed, uint32_t first, uint32_t count, uint8_t *levels,
                      uint8_t *n_gpus, uint16_t *free_mask, uint8_t *class_out, uint8_t *access_cost,
                      uint16_t *sibling_mask);
+/* event traces of config 2 (arrivals only, k uniform 1..8) and config 5 (arrival p = 0.55, else departure) */
+int gt_synth_events(int config, uint64_t seed, uint32_t n_events, uint8_t *ev_k, uint32_t *ev_arg);
 
 #ifdef __cplusplus
 }

@@ -207,3 +207,42 @@ def test_sharded_contexts_agree_with_one_context(gt, oracle):
                 a.score_all(fetch=False)
                 keys.append(a.best_node(ks))
         assert (gt.merge_place(keys) == want).all()
+
+
+def test_schedule_config2_matches_oracle_replay(gt, oracle):
+    """BASELINE config 2 at full size: 1 000 DGX-1 nodes, 10 000 pods with k uniform on 1..8, placed one at a
+    time; every placement (node and GPU mask) equals the oracle's sequential loop."""
+    lv, n, fr, _ = gt.synth_cluster(2, 0x5EED0002, 0, 1000)
+    k, arg = gt.synth_events(2, 0x5EED0012, 10000)
+    wp, wn, wm, wfree = oracle.replay(lv, n, fr, oracle.lut(0), k, arg)
+    with gt.Allocator(1000) as a:
+        a.load_nodes(lv, n, fr)
+        placed, on, om = a.schedule(k, arg)
+        assert placed == wp and (on == wn).all() and (om == wm).all()
+        # the device tables follow the commit loop: a fresh scoring pass sees the final free masks
+        got = a.score_all()
+        want, _ = oracle.exhaustive_cluster(lv, n, wfree, oracle.lut(0), 8)
+        assert (got == want).all()
+
+
+def test_schedule_config5_replay_with_departures(gt, oracle):
+    """Config 5 trace (arrivals and departures) on a mixed cluster, 200 000 events."""
+    lv, n, fr, _ = gt.synth_cluster(4, 0x5EED0004, 0, 2000)
+    k, arg = gt.synth_events(5, 0x5EED0005, 200000)
+    wp, wn, wm, wfree = oracle.replay(lv, n, fr, oracle.lut(0), k, arg)
+    with gt.Allocator(2000) as a:
+        a.load_nodes(lv, n, fr)
+        placed, on, om = a.schedule(k, arg)
+        assert placed == wp and (on == wn).all() and (om == wm).all()
+        assert placed > 50000
+
+
+def test_schedule_per_event_gpu_path(gt, oracle):
+    """Without the memo table (GT_FLAG_NO_MEMO) every event re-scores the touched node on the GPU."""
+    lv, n, fr, _ = gt.synth_cluster(4, 77, 0, 300)
+    k, arg = gt.synth_events(5, 123, 1500)
+    wp, wn, wm, _ = oracle.replay(lv, n, fr, oracle.lut(0), k, arg)
+    with gt.Allocator(300, flags=gt.FLAG_NO_MEMO) as a:
+        a.load_nodes(lv, n, fr)
+        placed, on, om = a.schedule(k, arg)
+        assert placed == wp and (on == wn).all() and (om == wm).all()

@@ -69,3 +69,14 @@ def test_synth_cluster_matches_oracle(gt, oracle, config, seed):
         i = int(np.nonzero(cl == cls)[0][0])
         _, _, oac, osib = oracle.class_topology(int(cls))
         assert (ac[i] == oac).all() and (sib[i] == osib).all()
+
+
+@pytest.mark.parametrize("config,seed", [(2, 0x5EED0012), (5, 0x5EED0005)])
+def test_synth_events_match_oracle(gt, oracle, config, seed):
+    k, arg = gt.synth_events(config, seed, 20000)
+    ok, oarg = oracle.synth_events(config, seed, 20000)
+    assert (k == ok).all() and (arg == oarg).all()
+    if config == 5:
+        assert abs((k > 0).mean() - 0.55) < 0.02
+    else:
+        assert (k > 0).all() and k.max() == 8 and k.min() == 1
