@@ -26,6 +26,8 @@ EXPORTS = [
     "gt_best_node", "gt_allocate", "gt_commit", "gt_release", "gt_score_all_async", "gt_sync", "gt_stream",
     "gt_device_best", "gt_num_nodes", "gt_launch_count", "gt_count_subsets", "gt_time_kernel",
     "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static", "gt_schedule", "gt_synth_events",
+    "gt_parse_topo_matrix", "gt_annotation_encode", "gt_annotation_decode", "gt_group_encode", "gt_group_decode",
+    "gt_bind_annotations", "gt_ext_sort", "gt_ext_bind", "gt_plugin_allocate",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -99,6 +101,15 @@ def _lib():
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
     L.gt_schedule.argtypes = [C.c_void_p, u8p, u32p, C.c_uint32, u32p, u16p, u64p]
     L.gt_synth_events.argtypes = [C.c_int, C.c_uint64, C.c_uint32, u8p, u32p]
+    L.gt_parse_topo_matrix.argtypes = [C.c_char_p, C.c_size_t, u8p, u32p]
+    L.gt_annotation_encode.argtypes = [u8p, C.c_uint32, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.gt_annotation_decode.argtypes = [C.c_char_p, C.c_size_t, u8p, u32p]
+    L.gt_group_encode.argtypes = [C.c_uint16, C.c_char_p, C.c_size_t]
+    L.gt_group_decode.argtypes = [C.c_char_p, u16p]
+    L.gt_bind_annotations.argtypes = [C.c_uint16, C.c_int64, C.c_int, C.c_char_p, C.c_size_t]
+    L.gt_ext_sort.argtypes = [C.c_void_p, C.c_uint32, u8p]
+    L.gt_ext_bind.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int64, u16p, C.c_char_p, C.c_size_t]
+    L.gt_plugin_allocate.argtypes = [C.c_char_p, C.c_int64, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.gt_score_nodes_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
                                         C.c_char_p, C.c_size_t]
     _LIB = L
@@ -313,6 +324,130 @@ class Allocator:
 def place_fields(key):
     key = int(key)
     return key >> 48, (key >> 16) & 0xFFFFFFFF, key & 0xFFFF
+
+
+# ---------------------------------------------------------------- text formats around the path (host only)
+def parse_topo_matrix(text):
+    """`nvidia-smi topo -m` output -> (levels[256] u8, n_gpus).  design.md:27-29."""
+    raw = text.encode() if isinstance(text, str) else text
+    lv = np.zeros(256, np.uint8)
+    n = C.c_uint32(0)
+    rc = _lib().gt_parse_topo_matrix(raw, len(raw), _p(lv, u8p), C.byref(n))
+    if rc:
+        raise GtError(rc, "gt_parse_topo_matrix")
+    return lv, int(n.value)
+
+
+def annotation_encode(levels, n_gpus):
+    """Level matrix -> node annotation text, one 'GPU_<ABBR>_<i>_<j>: <description>' line per pair (design.md:78-82)."""
+    lv = np.ascontiguousarray(levels, np.uint8).reshape(256)
+    buf = C.create_string_buffer(8192)
+    ln = C.c_size_t(0)
+    rc = _lib().gt_annotation_encode(_p(lv, u8p), n_gpus, buf, len(buf), C.byref(ln))
+    if rc:
+        raise GtError(rc, "gt_annotation_encode")
+    return buf.value.decode()
+
+
+def annotation_decode(text):
+    raw = text.encode() if isinstance(text, str) else text
+    lv = np.zeros(256, np.uint8)
+    n = C.c_uint32(0)
+    rc = _lib().gt_annotation_decode(raw, len(raw), _p(lv, u8p), C.byref(n))
+    if rc:
+        raise GtError(rc, "gt_annotation_decode")
+    return lv, int(n.value)
+
+
+def group_encode(mask):
+    buf = C.create_string_buffer(64)
+    rc = _lib().gt_group_encode(mask, buf, len(buf))
+    if rc:
+        raise GtError(rc, "gt_group_encode")
+    return buf.value.decode()
+
+
+def group_decode(text):
+    m = C.c_uint16(0)
+    rc = _lib().gt_group_decode(text.encode(), C.byref(m))
+    if rc:
+        raise GtError(rc, "gt_group_decode")
+    return int(m.value)
+
+
+def bind_annotations(mask, assume_time, assigned=False):
+    buf = C.create_string_buffer(256)
+    rc = _lib().gt_bind_annotations(mask, assume_time, 1 if assigned else 0, buf, len(buf))
+    if rc:
+        raise GtError(rc, "gt_bind_annotations")
+    return dict(l.split(": ", 1) for l in buf.value.decode().splitlines())
+
+
+# design.md:92-113: the scheduler policy that points kube-scheduler at the extender
+EXTENDER_POLICY = {
+    "kind": "Policy", "apiVersion": "v1",
+    "extenders": [{
+        "urlPrefix": "http://127.0.0.1:32743/gputopology-scheduler", "PrioritizeVerb": "sort", "bindVerb": "bind",
+        "enableHttps": False, "nodeCacheCapable": True,
+        "managedResources": [{"name": "aliyun.com/gpu", "ignoredByScheduler": False}], "ignorable": False,
+    }],
+}
+RESOURCE_NAME = "aliyun.com/gpu"
+
+
+class Extender:
+    """Mirror of the reference's scheduler extender for this path (design.md:88-121): `sort` answers with a
+    HostPriorityList (score 0..10 per node name), `bind` picks the GPUs on the chosen node and returns the pod
+    annotations of design.md:229-231.  There is no filter verb (design.md:117)."""
+
+    def __init__(self, allocator, node_names):
+        self.alloc = allocator
+        self.names = list(node_names)
+        self.index = {n: i for i, n in enumerate(self.names)}
+        self.pods = {}     # pod uid -> (node index, mask): "the pods recorded on the device" design.md:234
+
+    def sort(self, gpu_count, node_names=None):
+        """ExtenderArgs{Pod, NodeNames} -> HostPriorityList [{Host, Score}] (nodeCacheCapable: names only)."""
+        L = self.alloc._L
+        scores = np.zeros(self.alloc.num_nodes, np.uint8)
+        self.alloc._ck(L.gt_ext_sort(self.alloc._h, gpu_count, _p(scores, u8p)), "gt_ext_sort")
+        names = self.names if node_names is None else node_names
+        return [{"Host": n, "Score": int(scores[self.index[n]])} for n in names]
+
+    def bind(self, pod_name, pod_namespace, pod_uid, node, gpu_count, now):
+        """ExtenderBindingArgs -> (ExtenderBindingResult, pod annotations)."""
+        L = self.alloc._L
+        mask = C.c_uint16(0)
+        buf = C.create_string_buffer(256)
+        if node not in self.index:
+            return {"Error": "unknown node %s" % node}, {}
+        rc = L.gt_ext_bind(self.alloc._h, self.index[node], gpu_count, now, C.byref(mask), buf, len(buf))
+        if rc:
+            return {"Error": "%s: %s" % (L.gt_strerror(rc).decode(), L.gt_last_error(self.alloc._h).decode())}, {}
+        self.pods[pod_uid] = (self.index[node], int(mask.value))
+        return {"Error": ""}, dict(l.split(": ", 1) for l in buf.value.decode().splitlines())
+
+    def pod_deleted(self, pod_uid):
+        node, mask = self.pods.pop(pod_uid)
+        self.alloc.release([node], [mask])
+
+
+class DevicePlugin:
+    """Mirror of the reference's device plugin for this path: Allocate reads the device list bind wrote and
+    returns it as NVIDIA_VISIBLE_DEVICES, flipping ALIYUN_COM_GPU_ASSIGNED to true (design.md:236-246)."""
+
+    resource_name = RESOURCE_NAME      # ListAndWatch advertises this resource (design.md:84-86)
+
+    @staticmethod
+    def allocate(pod_annotations, now):
+        text = "".join("%s: %s\n" % kv for kv in pod_annotations.items())
+        env = C.create_string_buffer(128)
+        ann = C.create_string_buffer(256)
+        rc = _lib().gt_plugin_allocate(text.encode(), now, env, len(env), ann, len(ann))
+        if rc:
+            raise GtError(rc, "gt_plugin_allocate")
+        k, v = env.value.decode().split("=", 1)
+        return {"Envs": {k: v}}, dict(l.split(": ", 1) for l in ann.value.decode().splitlines())
 
 
 def shard_bounds(total_nodes, rank, world):

@@ -85,6 +85,7 @@ struct gt_ctx {
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
+    uint8_t *d_scores = nullptr;
     // pinned host mirrors
     uint16_t *h_free = nullptr;
     uint8_t *h_ngpus = nullptr;
@@ -435,6 +436,7 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
+        GT_CUDA(c, cudaMalloc(&c->d_scores, N));
         GT_CUDA(c, cudaMemset(c->d_ngpus, 0, N));
         GT_CUDA(c, cudaMemset(c->d_free, 0, N * 2));
         GT_CUDA(c, cudaMemset(c->d_levels, 0, N * 256));
@@ -473,7 +475,7 @@ void gt_destroy(gt_ctx *c)
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_place);
-    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_ticket);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_ticket); cudaFree(c->d_scores);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     for (auto &g : c->step_exec)
@@ -961,6 +963,46 @@ int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t
     }
     if (out_placed) *out_placed = placed;
     return GT_OK;
+}
+
+// "sort" verb (design.md:99,118): one score 0..10 per node for a pod asking for m GPUs
+int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores)
+{
+    if (!c || !out_scores || m < 1 || m > 16) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    int rc = GT_OK;
+    if (!c->best_valid || !c->free_uploaded) rc = gt_score_all_async(c);
+    else if (!c->dirty.empty()) rc = gt_score_dirty(c);
+    if (rc != GT_OK) return rc;
+    if (!c->n_nodes) return GT_OK;
+    uint32_t cmax = 0;
+    for (int i = 1; i < 16; i++) cmax = std::max<uint32_t>(cmax, c->lut[i]);
+    gt::k_sort_scores<<<(c->n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, m, cmax,
+                                                                                         c->d_scores);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    GT_CUDA(c, cudaMemcpyAsync(out_scores, c->d_scores, c->n_nodes, cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GT_OK;
+}
+
+// "bind" verb (design.md:100,119,223-234): GPUs for the pod on the chosen node, commit, pod annotations
+int gt_ext_bind(gt_ctx *c, uint32_t node, uint32_t m, int64_t assume_time, uint16_t *out_mask, char *out_annotations,
+                size_t cap)
+{
+    if (!c || !out_mask) return GT_ERR_INVALID;
+    if (node >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_ext_bind: node id out of range%s");
+    int rc = GT_OK;
+    if (!c->best_valid || !c->free_uploaded) rc = gt_score_all(c, nullptr);
+    else if (c->dirty_flag[node]) rc = gt_score_dirty(c);
+    if (rc != GT_OK) return rc;
+    uint16_t mask = 0, cost = 0;
+    if ((rc = gt_allocate(c, node, m, &mask, &cost)) != GT_OK) return rc;
+    if (mask == 0) return fail(c, GT_ERR_STATE, "gt_ext_bind: fewer free GPUs than requested%s");
+    if ((rc = gt_commit(c, &node, &mask, 1)) != GT_OK) return rc;
+    *out_mask = mask;
+    if (out_annotations && cap) rc = gt_bind_annotations(mask, assume_time, 0, out_annotations, cap);
+    return rc;
 }
 
 int gt_synth_events(int config, uint64_t seed, uint32_t n_events, uint8_t *ev_k, uint32_t *ev_arg)

@@ -696,6 +696,22 @@ __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t ite
     if (r == 0x12345678u) out[0] = r;
 }
 
+// ---------------------------------------------------------------- "sort" verb: HostPriority scores 0..10
+// score = floor(10 * (cmax*len - cost) / (cmax*len)), len = C(m,2) (design.md:205-217); infeasible -> 0
+__global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict__ best, uint32_t n, uint32_t m,
+                                                      uint32_t cmax, uint8_t *__restrict__ scores)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t b = best[(size_t)i * 16 + (m - 1)];
+    uint32_t sc = 0;
+    if (b != kInf) {
+        const uint32_t den = cmax * (m * (m - 1) / 2), cost = b >> 16;
+        sc = den == 0 ? 10u : (cost >= den ? 0u : (10u * (den - cost)) / den);
+    }
+    scores[i] = (uint8_t)sc;
+}
+
 // launch-cadence probes for profiling (no work)
 __global__ void k_noop(uint32_t *out) { if (out == nullptr && threadIdx.x == 9999) out[0] = 0; }
 __global__ void __launch_bounds__(128, 4) k_noop_smem(uint32_t *out)

@@ -128,6 +128,29 @@ int gt_release(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32
 int gt_schedule(gt_ctx *ctx, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
                 uint16_t *out_mask, uint64_t *out_placed);
 
+/* ---- the extender / device-plugin surface around the path (text formats are host only) ---- */
+/* replaces: topology discovery output design.md:27-29 -- the `nvidia-smi topo -m` table
+ * (imgs/gpu_topology_on_machine.png) -> 16x16 level codes.  NV# with # > 4 maps to GT_LV_NVS. */
+int gt_parse_topo_matrix(const char *text, size_t len, uint8_t out_levels[256], uint32_t *out_n);
+/* replaces: node annotations "GPU_<ABBR>_<i>_<j>: <description>" design.md:78-82 (one line per pair i<j) */
+int gt_annotation_encode(const uint8_t levels[256], uint32_t n_gpus, char *out, size_t cap, size_t *out_len);
+int gt_annotation_decode(const char *text, size_t len, uint8_t out_levels[256], uint32_t *out_n);
+/* replaces: ALIYUN_COM_GPU_GROUP value "0,1,2,3" design.md:231 */
+int gt_group_encode(uint16_t mask, char *out, size_t cap);
+int gt_group_decode(const char *text, uint16_t *out_mask);
+/* replaces: the pod annotations bind writes design.md:229-231 (assigned = 0) */
+int gt_bind_annotations(uint16_t mask, int64_t assume_time, int assigned, char *out, size_t cap);
+/* replaces: PrioritizeVerb "sort" reply design.md:99,118: score 0..10 per node (HostPriorityList) for a pod
+ * asking for m GPUs; re-scores whatever changed first.  out_scores: n_nodes bytes. */
+int gt_ext_sort(gt_ctx *ctx, uint32_t m, uint8_t *out_scores);
+/* replaces: bindVerb "bind" design.md:100,119,223-234: choose the GPUs on `node`, commit, format annotations */
+int gt_ext_bind(gt_ctx *ctx, uint32_t node, uint32_t m, int64_t assume_time, uint16_t *out_mask,
+                char *out_annotations, size_t cap);
+/* replaces: device plugin Allocate design.md:236-246: GROUP annotation -> "NVIDIA_VISIBLE_DEVICES=0,1"
+ * and the updated ASSIGNED / ASSUME_TIME annotations */
+int gt_plugin_allocate(const char *pod_annotations, int64_t now, char *out_env, size_t env_cap,
+                       char *out_annotations, size_t ann_cap);
+
 /* ---- asynchronous / measurement surface ---- */
 int gt_score_all_async(gt_ctx *ctx);     /* enqueue scoring + cluster argmin, no copies, no sync */
 int gt_sync(gt_ctx *ctx);

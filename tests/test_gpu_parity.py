@@ -246,3 +246,54 @@ def test_schedule_per_event_gpu_path(gt, oracle):
         a.load_nodes(lv, n, fr)
         placed, on, om = a.schedule(k, arg)
         assert placed == wp and (on == wn).all() and (om == wm).all()
+
+
+def test_extender_sort_bind_allocate_flow(gt, oracle):
+    """The reference's flow (imgs/gpu_topology_on_k8s.png steps 3-7) through the mirror: sort -> host choice ->
+    bind -> Allocate, against the oracle's sequential loop, on real topologies parsed from text fixtures."""
+    import os
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    tiles = [gt.parse_topo_matrix(open(os.path.join(gold, f + ".topo.txt")).read())
+             for f in ("f1_ring", "dgx1", "f2_pcie", "f3_tree4")]
+    N = 40
+    lv = np.stack([tiles[i % 4][0] for i in range(N)])
+    n = np.array([tiles[i % 4][1] for i in range(N)], np.uint8)
+    free = np.array([(1 << int(x)) - 1 for x in n], np.uint16)
+    names = ["node-%02d" % i for i in range(N)]
+    lut = oracle.lut(0)
+    cmax = oracle.cmax(lut)
+    rng = np.random.RandomState(9)
+    with gt.Allocator(N) as a:
+        a.load_nodes(lv, n, free)
+        ext = gt.Extender(a, names)
+        for pod in range(120):
+            m = int(rng.randint(1, 9))
+            prio = ext.sort(m)
+            want_best, _ = oracle.exhaustive_cluster(lv, n, free, lut, 2)
+            for i, hp in enumerate(prio):
+                b = int(want_best[i, m - 1])
+                want_score = 0 if b == ol.INFEASIBLE else oracle.score_int(b >> 16, m * (m - 1) // 2, cmax)
+                assert hp == {"Host": names[i], "Score": want_score}
+            key = int(oracle.cluster_argmin(want_best)[m - 1])
+            if key == gt.NO_PLACE:
+                res, ann = ext.bind("p%d" % pod, "default", "uid-%d" % pod, names[0], m, 1000 + pod)
+                if bin(int(free[0])).count("1") < m:
+                    assert res["Error"]
+                    continue
+            cost, node, mask = gt.place_fields(key) if key != gt.NO_PLACE else (0, 0, 0)
+            if key == gt.NO_PLACE:
+                continue
+            res, ann = ext.bind("p%d" % pod, "default", "uid-%d" % pod, names[node], m, 1000 + pod)
+            assert res == {"Error": ""}
+            assert ann == {"ALIYUN_COM_GPU_ASSIGNED": "false", "ALIYUN_COM_GPU_ASSUME_TIME": str(1000 + pod),
+                           "ALIYUN_COM_GPU_GROUP": gt.group_encode(mask)}
+            free[node] &= ~mask & 0xFFFF
+            reply, upd = gt.DevicePlugin.allocate(ann, 2000 + pod)
+            assert reply["Envs"]["NVIDIA_VISIBLE_DEVICES"] == gt.group_encode(mask)
+            assert upd["ALIYUN_COM_GPU_ASSIGNED"] == "true"
+            if pod % 5 == 4:      # a pod finishes
+                uid = sorted(ext.pods)[0]
+                nd, mk = ext.pods[uid]
+                ext.pod_deleted(uid)
+                free[nd] |= mk
+        assert ext.bind("x", "default", "uid-x", "no-such-node", 1, 0)[0]["Error"]
