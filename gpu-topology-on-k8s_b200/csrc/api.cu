@@ -233,6 +233,17 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     return GT_OK;
 }
 
+// request-size-1 policy of the Gaia paper, applied after K1 (no-op for the default policy)
+int launch_singular(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *place)
+{
+    if (c->k1_policy != GT_K1_GAIA_SINGULAR || !n) return GT_OK;
+    gt::k_singular<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+        c->d_ngpus, c->d_free, c->d_access, c->d_sibling, d_ids, n, c->d_best, place, c->first_node);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
 // Multi-GPU: min of the 16 placement keys over all ranks, on the communication stream.  The pass that
 // produced `place` is ordered before it by an event; consumers wait for ev_comm[parity].
 int nccl_min(gt_ctx *c, unsigned long long *place, uint32_t parity)
@@ -269,6 +280,7 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
         GT_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
         int rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, parity));
         if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, parity));
+        if (rc == GT_OK) rc = launch_singular(c, nullptr, c->n_nodes, bin_place(c, parity));
         cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
         c->launches = before;
         if (rc != GT_OK || e != cudaSuccess || !graph) {
@@ -286,7 +298,7 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
         c->step_nodes = c->n_nodes;
     }
     GT_CUDA(c, cudaGraphLaunch(c->step_exec[parity], c->stream));
-    c->launches += 2;
+    c->launches += c->k1_policy == GT_K1_GAIA_SINGULAR ? 3 : 2;
     c->place_cur = bin_place(c, parity);
     return GT_OK;
 }
@@ -332,6 +344,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     if (!d_ids && n) {
         if (c->flags & GT_FLAG_FUSED_CHUNKS) {
             if ((rc = launch_prioritize(c)) != GT_OK) return rc;
+            if ((rc = launch_singular(c, nullptr, n, c->place_cur)) != GT_OK) return rc;
             if (c->comm) {   // the chunk kernel reuses its two buffers every other launch: exchange in stream order
                 NcclApi *api = nccl_api();
                 int e = api->AllReduce(c->place_cur, c->place_cur, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
@@ -349,11 +362,13 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
         if (!done) {
             if ((rc = launch_bin(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
             if ((rc = launch_score(c, n, bin_place(c, par))) != GT_OK) return rc;
+            if ((rc = launch_singular(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
         }
     } else {
         if (n) {
             if ((rc = launch_bin(c, d_ids, n, nullptr)) != GT_OK) return rc;
             if ((rc = launch_score(c, n, nullptr)) != GT_OK) return rc;
+            if ((rc = launch_singular(c, d_ids, n, nullptr)) != GT_OK) return rc;
         }
         if ((rc = launch_argmin(c)) != GT_OK) return rc;
     }
@@ -514,10 +529,15 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
     memcpy(c->h_ngpus + first, n_gpus, count);
     memcpy(c->h_free + first, free_mask, (size_t)count * 2);
     {   // topology classes: nodes with the same level matrix and GPU count share one memo table
-        std::string key(257, '\0');
+        const bool gaia = c->k1_policy == GT_K1_GAIA_SINGULAR;
+        std::string key(gaia ? 257 + 16 + 32 : 257, '\0');
         for (uint32_t i = 0; i < count; i++) {
             memcpy(&key[0], levels + (size_t)i * 256, 256);
             key[256] = (char)n_gpus[i];
+            if (gaia) {   // the request-1 policy reads per-GPU access costs and sibling sets: part of the class
+                if (access_cost) memcpy(&key[257], access_cost + (size_t)i * 16, 16);
+                if (sibling_mask) memcpy(&key[273], sibling_mask + (size_t)i * 16, 32);
+            }
             auto it = c->class_of_tile.find(key);
             if (it == c->class_of_tile.end()) {
                 it = c->class_of_tile.emplace(key, (uint32_t)c->class_tile.size()).first;
@@ -809,6 +829,10 @@ int build_memo(gt_ctx *c)
     cfg.struct_size = sizeof cfg;
     cfg.device = c->device;
     cfg.max_nodes = (uint32_t)rows;
+    cfg.k1_policy = c->k1_policy;
+    const bool gaia = c->k1_policy == GT_K1_GAIA_SINGULAR;
+    std::vector<uint8_t> ac;
+    std::vector<uint16_t> sb;
     gt_ctx *m = nullptr;
     int rc = gt_create(&cfg, &m);
     if (rc != GT_OK) return fail(c, rc, "gt_schedule: memo context: %s", gt_strerror(rc));
@@ -826,8 +850,15 @@ int build_memo(gt_ctx *c)
                 memcpy(&lv[i * 256], c->class_tile[k].data(), 256);
                 fr[i] = (uint16_t)(b0 + i);
             }
-            rc = gt_load_nodes(m, (uint32_t)(c->memo_off[k] + b0), (uint32_t)bn, lv.data(), ng.data(), nullptr, nullptr,
-                               fr.data());
+            if (gaia) {
+                ac.resize(bn * 16); sb.resize(bn * 16);
+                for (size_t i = 0; i < bn; i++) {
+                    memcpy(&ac[i * 16], c->class_tile[k].data() + 257, 16);
+                    memcpy(&sb[i * 16], c->class_tile[k].data() + 273, 32);
+                }
+            }
+            rc = gt_load_nodes(m, (uint32_t)(c->memo_off[k] + b0), (uint32_t)bn, lv.data(), ng.data(),
+                               gaia ? ac.data() : nullptr, gaia ? sb.data() : nullptr, fr.data());
         }
     }
     if (rc == GT_OK) {

@@ -696,6 +696,42 @@ __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t ite
     if (r == 0x12345678u) out[0] = r;
 }
 
+// ---------------------------------------------------------------- Gaia Alg. 3 "Singular" for request size 1
+// gpu_scheduler_algorithm_1.png: candidates = free GPUs that have siblings and whose siblings are all used;
+// lowest access cost (then lowest id) wins; without candidates the free GPU with the lowest access cost.
+// Overrides best[node][0] (cost stays 0) and, for the node that holds the k = 1 placement key, its mask.
+__global__ void __launch_bounds__(kCta) k_singular(const uint8_t *__restrict__ n_gpus,
+                                                   const uint16_t *__restrict__ free_mask,
+                                                   const uint8_t *__restrict__ access,
+                                                   const uint16_t *__restrict__ sibling,
+                                                   const uint32_t *__restrict__ ids, uint32_t n,
+                                                   uint32_t *__restrict__ best, unsigned long long *place,
+                                                   uint32_t first_node)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t node = ids ? ids[i] : i;
+    uint32_t ng = n_gpus[node];
+    ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
+    const uint32_t f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
+    if (!f) return;
+    int pick = -1, pick_any = -1;
+    uint32_t cost = 0xFFFFFFFFu, cost_any = 0xFFFFFFFFu;
+    for (uint32_t r = f; r; r &= r - 1) {
+        const int g = __ffs(r) - 1;
+        const uint32_t ac = access[(size_t)node * 16 + g], sib = sibling[(size_t)node * 16 + g];
+        if (ac < cost_any) { cost_any = ac; pick_any = g; }
+        if (sib != 0 && (sib & f) == 0 && ac < cost) { cost = ac; pick = g; }
+    }
+    const uint32_t v = 1u << (pick >= 0 ? pick : pick_any);
+    best[(size_t)node * 16] = v;
+    if (place) {
+        const unsigned long long key = place[0];
+        if (key != ~0ull && (uint32_t)((key >> 16) & 0xFFFFFFFFu) == first_node + node)
+            place[0] = (key & ~0xFFFFull) | v;
+    }
+}
+
 // ---------------------------------------------------------------- "sort" verb: HostPriority scores 0..10
 // score = floor(10 * (cmax*len - cost) / (cmax*len)), len = C(m,2) (design.md:205-217); infeasible -> 0
 __global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict__ best, uint32_t n, uint32_t m,

@@ -297,3 +297,47 @@ def test_extender_sort_bind_allocate_flow(gt, oracle):
                 ext.pod_deleted(uid)
                 free[nd] |= mk
         assert ext.bind("x", "default", "uid-x", "no-such-node", 1, 0)[0]["Error"]
+
+
+def test_gaia_singular_policy_on_device(gt, oracle):
+    """GT_K1_GAIA_SINGULAR: request size 1 follows Gaia Alg. 3 (KA3, KA4a, KA5 and a sweep over every free mask of
+    the tree topologies); every other request size is unchanged."""
+    for cls, n_expected in (("F2_PCIE", 8), ("F3_TREE4", 4), ("DGX1", 8)):
+        lv, n, ac, sib = oracle.class_topology(ol.CLS[cls])
+        N = 1 << n
+        levels = np.tile(lv, (N, 1))
+        free = np.arange(N, dtype=np.uint16)
+        with gt.Allocator(N, k1_policy=gt.K1_GAIA_SINGULAR) as a:
+            a.load_nodes(levels, np.full(N, n, np.uint8), free, access_cost=np.tile(ac, (N, 1)),
+                         sibling_mask=np.tile(sib, (N, 1)))
+            got = a.score_all()
+            want, _ = oracle.exhaustive_cluster(levels, np.full(N, n, np.uint8), free, oracle.lut(0), 4)
+            for f in range(1, N):
+                want[f, 0] = 1 << oracle.gaia_singular(n, f, ac, sib)
+            assert (got == want).all()
+            place = a.best_node([1, 2])
+            assert gt.place_fields(place[0]) == (0, 1, int(want[1, 0]) & 0xFFFF)
+            assert int(place[1]) == int(oracle.cluster_argmin(want)[1])
+            # dirty path keeps the policy
+            a.commit([N - 1], [1])
+            a.score_dirty()
+            got2 = a.score_all()
+            want[N - 1] = want[N - 2]
+            assert (got2 == want).all()
+    # the documented answers
+    lv, n, ac, sib = oracle.class_topology(ol.CLS["F2_PCIE"])
+    with gt.Allocator(1, k1_policy=gt.K1_GAIA_SINGULAR) as a:
+        a.load_nodes(lv[None, :], [8], [0xFF & ~((1 << 4) | (1 << 6))], access_cost=ac[None, :], sibling_mask=sib[None, :])
+        a.score_all()
+        assert a.allocate(0, 1)[0] == 1 << 5            # KA3: GPU5
+    lv, n, ac, sib = oracle.class_topology(ol.CLS["F3_TREE4"])
+    with gt.Allocator(2, k1_policy=gt.K1_GAIA_SINGULAR) as a:
+        a.load_nodes(np.tile(lv, (2, 1)), [4, 4], [0xF, 0xF & ~4], access_cost=np.tile(ac, (2, 1)),
+                     sibling_mask=np.tile(sib, (2, 1)))
+        a.score_all()
+        assert a.allocate(0, 1)[0] in (1 << 2, 1 << 3)  # KA4a
+        assert a.allocate(1, 1)[0] == 1 << 3            # KA5
+        assert a.allocate(1, 2)[0] == 0b0011            # KA6
+        # the commit loop keeps the policy too: a k = 1 pod on node 1 (cousin of GPU3 is used) takes GPU3 first
+        placed, on, om = a.schedule(np.array([1], np.uint8), np.array([0], np.uint32))
+        assert placed == 1 and int(on[0]) == 0 and int(om[0]) in (4, 8)
