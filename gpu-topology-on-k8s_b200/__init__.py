@@ -18,7 +18,7 @@ NO_PLACE = 0xFFFFFFFFFFFFFFFF
 LV = dict(X=0, NVS=1, NV4=2, NV3=3, NV2=4, NV1=5, PSB=6, PIX=7, PXB=8, PHB=9, NODE=10, SYS=11)
 LUT_DEFAULT, LUT_DESIGN_MARKS = 0, 1
 K1_FIRST_UNUSED, K1_GAIA_SINGULAR = 0, 1
-FLAG_FUSED_CHUNKS, FLAG_NO_GRAPH, FLAG_NO_MEMO = 1, 2, 4
+FLAG_NO_GRAPH, FLAG_NO_MEMO = 2, 4
 
 EXPORTS = [
     "gt_create", "gt_destroy", "gt_strerror", "gt_last_error", "gt_lut_preset", "gt_set_cost_lut",
@@ -107,7 +107,7 @@ def _lib():
     L.gt_group_encode.argtypes = [C.c_uint16, C.c_char_p, C.c_size_t]
     L.gt_group_decode.argtypes = [C.c_char_p, u16p]
     L.gt_bind_annotations.argtypes = [C.c_uint16, C.c_int64, C.c_int, C.c_char_p, C.c_size_t]
-    L.gt_ext_sort.argtypes = [C.c_void_p, C.c_uint32, u8p]
+    L.gt_ext_sort.argtypes = [C.c_void_p, C.c_uint32, u8p, u64p]
     L.gt_ext_bind.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int64, u16p, C.c_char_p, C.c_size_t]
     L.gt_plugin_allocate.argtypes = [C.c_char_p, C.c_int64, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.gt_score_nodes_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
@@ -262,6 +262,10 @@ class Allocator:
     def score_all_into(self, host_ptr):
         self._ck(self._L.gt_score_all(self._h, host_ptr), "gt_score_all")
 
+    def ext_sort_into(self, gpu_count, scores, place=None):
+        """`sort` verb into a caller buffer (numpy u8[n_nodes], ideally pinned); place: optional u64[16]."""
+        self._ck(self._L.gt_ext_sort(self._h, gpu_count, _p(scores, u8p), _p(place, u64p)), "gt_ext_sort")
+
     def score_dirty(self):
         self._ck(self._L.gt_score_dirty(self._h), "gt_score_dirty")
 
@@ -410,7 +414,7 @@ class Extender:
         """ExtenderArgs{Pod, NodeNames} -> HostPriorityList [{Host, Score}] (nodeCacheCapable: names only)."""
         L = self.alloc._L
         scores = np.zeros(self.alloc.num_nodes, np.uint8)
-        self.alloc._ck(L.gt_ext_sort(self.alloc._h, gpu_count, _p(scores, u8p)), "gt_ext_sort")
+        self.alloc._ck(L.gt_ext_sort(self.alloc._h, gpu_count, _p(scores, u8p), None), "gt_ext_sort")
         names = self.names if node_names is None else node_names
         return [{"Host": n, "Score": int(scores[self.index[n]])} for n in names]
 

@@ -69,10 +69,8 @@ struct gt_ctx {
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
     uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
-    unsigned long long *d_place = nullptr;      // [4][16]: two parities of the chunk kernel, two of the K0+K1 path
+    unsigned long long *d_place = nullptr;      // [4][16]: [2],[3] = the two parities of the K0+K1 path, [0] NCCL warm-up
     unsigned long long *place_cur = nullptr;    // where the latest placement keys are
-    uint32_t *d_ticket = nullptr;               // [2] chunk tickets of the fused kernel
-    uint32_t parity = 0;
     cudaGraphExec_t step_exec[2] = {nullptr, nullptr};   // captured K0 + K1 of a full pass, per place parity
     uint32_t step_nodes = 0;                    // n_nodes the graphs were captured for
     bool graph_failed = false;
@@ -316,44 +314,14 @@ int launch_argmin(gt_ctx *c)
     return GT_OK;
 }
 
-// the fused kernel: K0 + K1 + K2 of every loaded node in one launch
-int launch_prioritize(gt_ctx *c)
-{
-    gt::PrioParams p;
-    p.cost = c->d_cost; p.n_gpus = c->d_ngpus; p.free_mask = c->d_free; p.best = c->d_best;
-    p.place = c->d_place; p.ticket = c->d_ticket;
-    p.n_nodes = c->n_nodes; p.first_node = c->first_node; p.parity = c->parity;
-    const uint32_t chunks = (c->n_nodes + gt::kChunk - 1) / gt::kChunk;
-    const uint32_t grid = std::max(1u, std::min<uint32_t>(chunks, (uint32_t)c->num_sms * 4));
-    gt::k_prioritize<<<grid, gt::kChunk, 0, c->stream>>>(p);
-    c->launches++;
-    GT_CUDA(c, cudaGetLastError());
-    c->place_cur = c->d_place + c->parity * 16;
-    c->parity ^= 1u;
-    return GT_OK;
-}
-
-// Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1 (or, with
-// GT_FLAG_FUSED_CHUNKS, the single-launch chunk kernel).  Listed (dirty) nodes: K0 + K1 over the list,
-// then K2 over the whole table.  n == 0: K2 only.
+// Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1, one graph launch.
+// Listed (dirty) nodes: K0 + K1 over the list, then K2 over the whole table.  n == 0: K2 only.
 int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
     int rc;
     const uint32_t par = c->bin_parity;
     if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
     if (!d_ids && n) {
-        if (c->flags & GT_FLAG_FUSED_CHUNKS) {
-            if ((rc = launch_prioritize(c)) != GT_OK) return rc;
-            if ((rc = launch_singular(c, nullptr, n, c->place_cur)) != GT_OK) return rc;
-            if (c->comm) {   // the chunk kernel reuses its two buffers every other launch: exchange in stream order
-                NcclApi *api = nccl_api();
-                int e = api->AllReduce(c->place_cur, c->place_cur, 16, kNcclUint64, kNcclMin, c->comm, c->stream);
-                if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce failed%s");
-                c->comm_last = -1;
-            }
-            c->best_valid = c->place_valid = true;
-            return GT_OK;
-        }
         bool done = false;
         if (!(c->flags & GT_FLAG_NO_GRAPH) && !c->graph_failed) {
             done = launch_step_graph(c, par) == GT_OK;
@@ -445,8 +413,6 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
         GT_CUDA(c, cudaMalloc(&c->d_place, 64 * sizeof(unsigned long long)));
         GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 64 * sizeof(unsigned long long)));
-        GT_CUDA(c, cudaMalloc(&c->d_ticket, 2 * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMemset(c->d_ticket, 0, 2 * sizeof(uint32_t)));
         c->place_cur = c->d_place + 32;
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
@@ -490,7 +456,7 @@ void gt_destroy(gt_ctx *c)
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_place);
-    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_ticket); cudaFree(c->d_scores);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_scores);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     for (auto &g : c->step_exec)
@@ -732,7 +698,6 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
         }
         if (w == "score") return launch_score(c, c->n_nodes, bin_place(c, 0), true);
         if (w == "argmin") return launch_argmin(c);
-        if (w == "prioritize") return launch_prioritize(c);
         if (w == "step") return enqueue_scoring(c, nullptr, c->n_nodes);
         if (w == "step_nograph") {
             int r2 = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
@@ -997,7 +962,7 @@ int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t
 }
 
 // "sort" verb (design.md:99,118): one score 0..10 per node for a pod asking for m GPUs
-int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores)
+int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
 {
     if (!c || !out_scores || m < 1 || m > 16) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
@@ -1013,7 +978,12 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores)
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     GT_CUDA(c, cudaMemcpyAsync(out_scores, c->d_scores, c->n_nodes, cudaMemcpyDeviceToHost, c->stream));
+    if (out_place) {   // the host choice for every request size rides on the same synchronisation
+        if (c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
+        GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    }
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (out_place) memcpy(out_place, c->h_place, 16 * sizeof(uint64_t));
     return GT_OK;
 }
 

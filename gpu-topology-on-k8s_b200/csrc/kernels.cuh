@@ -480,198 +480,6 @@ __global__ void __launch_bounds__(kCta) k_argmin(const uint32_t *__restrict__ be
     if (tid < 16 && s_min[tid] != ~0ull) atomicMin(&place[tid], s_min[tid]);
 }
 
-// ---------------------------------------------------------------- fused Prioritize: K0 + K1 + K2 in one launch
-// A CTA takes a chunk of 128 consecutive nodes: stages their cost tiles in shared memory with
-// coalesced 16-byte loads, sorts the chunk by p = popcount(free) (big nodes first, p descending), runs
-// the lane-per-subset-group enumeration for p > 8 and the thread-per-node trees for p <= 8, writes the
-// best rows and folds the chunk's minima into the cluster argmin.  No global scratch, no dependent
-// global loads after the staging, one launch per scheduling cycle.
-constexpr int kChunk = 128;
-
-struct PrioParams {
-    const uint8_t *cost;
-    const uint8_t *n_gpus;
-    const uint16_t *free_mask;
-    uint32_t *best;
-    unsigned long long *place;        // [2][16]: this launch folds into place[parity], resets place[parity^1]
-    uint32_t *ticket;                 // [2]: chunk ticket of this launch = ticket[parity], resets the other
-    uint32_t n_nodes, first_node, parity;
-};
-
-template <int P>
-__device__ __forceinline__ void score_small_tile(const uint8_t *tile, uint32_t f, uint32_t (&out)[16])
-{
-    if constexpr (P > 0) {
-        uint32_t pos[P], bit[P];
-#pragma unroll
-        for (int a = 0; a < P; a++) {
-            const int g = __ffs(f) - 1;
-            f &= f - 1;
-            pos[a] = (uint32_t)g;
-            bit[a] = 1u << g;
-        }
-        uint32_t c[P * P];
-#pragma unroll
-        for (int a = 0; a < P; a++)
-#pragma unroll
-            for (int b = 0; b < P; b++)
-                c[a * P + b] = (a < b) ? ((uint32_t)tile[pos[a] * 16 + pos[b]] << 16) : 0u;
-        uint32_t acc[P + 1], R[P];
-#pragma unroll
-        for (int k = 0; k <= P; k++) acc[k] = kInf;
-#pragma unroll
-        for (int a = 0; a < P; a++) R[a] = 0u;
-        Children<P, P, 0>::run(0u, R, c, bit, acc);
-#pragma unroll
-        for (int k = 1; k <= P; k++) out[k - 1] = acc[k];
-    }
-}
-
-__global__ void __launch_bounds__(kChunk, 4) k_prioritize(PrioParams prm)
-{
-    __shared__ __align__(16) uint8_t s_tile[kChunk * kTileStride];
-    __shared__ uint32_t s_best[kChunk][kBins];        // rows of the chunk's big nodes, by sorted slot
-    __shared__ unsigned long long s_place[16];
-    __shared__ uint32_t s_hist[kBins], s_base[kBins]; // nodes per p; first sorted slot of bin p
-    __shared__ uint32_t s_lane0[kBins];               // first big lane of bin p (p > 8)
-    __shared__ uint32_t s_chunk, s_nbig, s_lanes;
-    __shared__ uint16_t s_free[kChunk];
-    __shared__ uint8_t s_p[kChunk], s_order[kChunk];
-
-    const uint32_t tid = threadIdx.x;
-    if (tid < 16) s_place[tid] = ~0ull;
-    if (blockIdx.x == 0) {   // prepare the other parity for the next launch
-        if (tid < 16) prm.place[(prm.parity ^ 1u) * 16 + tid] = ~0ull;
-        if (tid == 16) prm.ticket[prm.parity ^ 1u] = 0u;
-    }
-    const uint32_t n_chunks = (prm.n_nodes + kChunk - 1) / kChunk;
-    for (;;) {
-        __syncthreads();                      // previous chunk fully consumed
-        if (tid == 0) s_chunk = atomicAdd(prm.ticket + prm.parity, 1u);
-        if (tid < kBins) s_hist[tid] = 0u;
-        __syncthreads();
-        const uint32_t chunk = s_chunk;
-        if (chunk >= n_chunks) break;
-        const uint32_t node0 = chunk * kChunk;
-        const uint32_t live = min((uint32_t)kChunk, prm.n_nodes - node0);
-
-        // ---- stage: free masks, p, cost tiles
-        int p = -1;
-        uint32_t binslot = 0;
-        if (tid < live) {
-            uint32_t ng = prm.n_gpus[node0 + tid];
-            ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-            const uint32_t f = (uint32_t)prm.free_mask[node0 + tid] & ((1u << ng) - 1u);
-            p = __popc(f);
-            s_free[tid] = (uint16_t)f;
-            s_p[tid] = (uint8_t)p;
-            binslot = atomicAdd(&s_hist[p], 1u);
-        }
-        {
-            const uint4 *src = reinterpret_cast<const uint4 *>(prm.cost + (size_t)node0 * 256);
-            uint4 v[16];
-#pragma unroll
-            for (int i = 0; i < 16; i++) {
-                const uint32_t idx = (uint32_t)i * kChunk + tid;       // 16-byte piece within the chunk
-                v[i] = ((idx >> 4) < live) ? __ldg(src + idx) : make_uint4(0, 0, 0, 0);
-            }
-#pragma unroll
-            for (int i = 0; i < 16; i++) {
-                const uint32_t idx = (uint32_t)i * kChunk + tid;
-                *reinterpret_cast<uint4 *>(s_tile + (idx >> 4) * kTileStride + (idx & 15u) * 16) = v[i];
-            }
-        }
-        __syncthreads();
-        // ---- sort by p descending: slots [0, nbig) are p = 16..9, then p = 8..0
-        if (tid == 0) {
-            uint32_t slot = 0, lanes = 0;
-            for (int q = 16; q >= 0; q--) {
-                s_base[q] = slot;
-                s_lane0[q] = lanes;
-                slot += s_hist[q];
-                if (q > 8) lanes += s_hist[q] << (q - 8);
-                if (q == 9) s_nbig = slot;
-            }
-            s_lanes = lanes;
-        }
-        __syncthreads();
-        if (p >= 0) s_order[s_base[p] + binslot] = (uint8_t)tid;
-        const uint32_t nbig = s_nbig, lanes = s_lanes;
-        for (uint32_t e = tid; e < nbig * kBins; e += kChunk) (&s_best[0][0])[e] = kInf;
-        __syncthreads();
-
-        // ---- big nodes: 2^(p-8) lanes each, packed back to back
-        for (uint32_t id = tid; id < lanes; id += kChunk) {
-            int q = 16;
-            while (q > 9 && id >= s_lane0[q - 1]) q--;      // s_lane0 grows as q falls
-            const uint32_t rel = id - s_lane0[q];
-            const int hb = q - 8;
-            const uint32_t slot = s_base[q] + (rel >> hb);
-            const uint32_t h = rel & ((1u << hb) - 1u);
-            const uint32_t nl = s_order[slot];
-            score_big_lane(s_tile + nl * kTileStride, s_free[nl], hb, h, &s_best[slot][0]);
-        }
-        __syncthreads();
-        for (uint32_t e = tid; e < nbig * 16; e += kChunk) {
-            const uint32_t slot = e >> 4, k = e & 15u;
-            const uint32_t v = s_best[slot][k + 1];
-            const uint32_t node = node0 + s_order[slot];
-            prm.best[(size_t)node * 16 + k] = v;
-            if (v != kInf) {
-                const unsigned long long key = ((unsigned long long)(v >> 16) << 48) |
-                                               ((unsigned long long)(prm.first_node + node) << 16) | (v & 0xFFFFu);
-                atomicMin(&s_place[k], key);
-            }
-        }
-
-        // ---- small nodes: one thread each, p descending so warps are nearly uniform
-        {
-            const uint32_t nsmall = live - nbig;
-            uint32_t out[16];
-#pragma unroll
-            for (int k = 0; k < 16; k++) out[k] = kInf;
-            uint32_t nl = 0xFFFFu;
-            if (tid < nsmall) {
-                nl = s_order[nbig + tid];
-                const uint8_t *tile = s_tile + nl * kTileStride;
-                const uint32_t f = s_free[nl];
-                switch (s_p[nl]) {
-                case 1: score_small_tile<1>(tile, f, out); break;
-                case 2: score_small_tile<2>(tile, f, out); break;
-                case 3: score_small_tile<3>(tile, f, out); break;
-                case 4: score_small_tile<4>(tile, f, out); break;
-                case 5: score_small_tile<5>(tile, f, out); break;
-                case 6: score_small_tile<6>(tile, f, out); break;
-                case 7: score_small_tile<7>(tile, f, out); break;
-                case 8: score_small_tile<8>(tile, f, out); break;
-                default: break;
-                }
-                uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)(node0 + nl) * 16);
-                o[0] = make_uint4(out[0], out[1], out[2], out[3]);
-                o[1] = make_uint4(out[4], out[5], out[6], out[7]);
-                o[2] = make_uint4(kInf, kInf, kInf, kInf);
-                o[3] = make_uint4(kInf, kInf, kInf, kInf);
-            }
-            // chunk minimum per k: lowest cost, then lowest node -> two 32-bit warp reductions
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const uint32_t cmin = __reduce_min_sync(0xFFFFFFFFu, out[k] & 0xFFFF0000u);
-                if (cmin != kInf) {    // warp-uniform
-                    const uint32_t cand = ((out[k] & 0xFFFF0000u) == cmin) ? nl : 0xFFFFFFFFu;
-                    const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, cand);
-                    if (nl == nmin) {
-                        const unsigned long long key = ((unsigned long long)(cmin >> 16) << 48) |
-                            ((unsigned long long)(prm.first_node + node0 + nl) << 16) | (out[k] & 0xFFFFu);
-                        atomicMin(&s_place[k], key);
-                    }
-                }
-            }
-        }
-    }
-    // the break above happens right after a barrier: s_place is complete for this CTA
-    if (tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + prm.parity * 16 + tid, s_place[tid]);
-}
-
 // ---------------------------------------------------------------- INT32 add peak (roofline denominator)
 // 8 independent IADD chains per thread; ops = grid*block*iters*8*unroll
 __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t iters, uint32_t seed)

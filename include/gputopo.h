@@ -56,8 +56,7 @@ enum {
 };
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
 enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
-/* GT_FLAG_FUSED_CHUNKS: full passes use the single-launch chunk kernel instead of K0 + K1 (same results) */
-enum { GT_FLAG_FUSED_CHUNKS = 1, GT_FLAG_NO_GRAPH = 2 /* launch K0, K1 one by one instead of as a CUDA graph */,
+enum { GT_FLAG_NO_GRAPH = 2 /* launch K0, K1 one by one instead of as a CUDA graph */,
        GT_FLAG_NO_MEMO = 4 /* gt_schedule re-scores on the GPU per event instead of using the memo table */ };
 
 typedef struct gt_ctx gt_ctx;
@@ -141,8 +140,9 @@ int gt_group_decode(const char *text, uint16_t *out_mask);
 /* replaces: the pod annotations bind writes design.md:229-231 (assigned = 0) */
 int gt_bind_annotations(uint16_t mask, int64_t assume_time, int assigned, char *out, size_t cap);
 /* replaces: PrioritizeVerb "sort" reply design.md:99,118: score 0..10 per node (HostPriorityList) for a pod
- * asking for m GPUs; re-scores whatever changed first.  out_scores: n_nodes bytes. */
-int gt_ext_sort(gt_ctx *ctx, uint32_t m, uint8_t *out_scores);
+ * asking for m GPUs; re-scores whatever changed first.  out_scores: n_nodes bytes.  out_place: optional,
+ * 16 placement keys (as gt_best_node for k = 1..16) fetched in the same synchronisation. */
+int gt_ext_sort(gt_ctx *ctx, uint32_t m, uint8_t *out_scores, uint64_t *out_place);
 /* replaces: bindVerb "bind" design.md:100,119,223-234: choose the GPUs on `node`, commit, format annotations */
 int gt_ext_bind(gt_ctx *ctx, uint32_t node, uint32_t m, int64_t assume_time, uint16_t *out_mask,
                 char *out_annotations, size_t cap);
@@ -161,7 +161,7 @@ uint64_t gt_launch_count(const gt_ctx *ctx);   /* kernels this context has launc
 /* candidate subsets one full scoring pass covers: sum over nodes of 2^popcount(free)-1; optionally
  * the algorithmic pair-cost additions sum C(f,2)*2^(f-2) */
 int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds);
-/* time `iters` back-to-back launches of one kernel ("step", "bin", "score", "argmin", "prioritize", "int32_peak") with
+/* time `iters` back-to-back launches of one kernel ("step", "step_nograph", "bin", "score", "argmin", "int32_peak") with
  * CUDA events on the context's stream; out_ms = average per launch */
 int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
 
