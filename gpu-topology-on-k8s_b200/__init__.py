@@ -62,9 +62,11 @@ def _lib():
     global _LIB
     if _LIB is not None:
         return _LIB
-    so = lib_path()
-    if _build.stale():
-        _build.build()
+    so = os.environ.get("GT_LIB")      # profiling aid: load another build of the same ABI
+    if not so:
+        so = lib_path()
+        if _build.stale():
+            _build.build()
     L = C.CDLL(so)
     L.gt_strerror.restype = C.c_char_p
     L.gt_last_error.restype = C.c_char_p
