@@ -94,6 +94,8 @@ struct gt_ctx {
     std::vector<uint8_t> dirty_flag;
     std::vector<uint32_t> dirty;
     bool free_uploaded = true;    // device free[] equals the mirror except for `dirty`
+    cudaEvent_t ev_h2d = nullptr; // last copy that reads the pinned mirrors (they may not change before it ran)
+    bool h2d_pending = false;
     bool best_valid = false, place_valid = false;
     uint64_t launches = 0;
     void *comm = nullptr;
@@ -151,17 +153,31 @@ __global__ void k_scatter_free(const uint32_t *ids, const uint16_t *masks, uint3
     if (i < n) free_mask[ids[i]] = masks[i];
 }
 
+// the pinned mirrors are about to be modified: a copy that still reads them must have run
+int mirror_writable(gt_ctx *c)
+{
+    if (c->h2d_pending) {
+        GT_CUDA(c, cudaEventSynchronize(c->ev_h2d));
+        c->h2d_pending = false;
+    }
+    return GT_OK;
+}
+
 // bring the device free[] up to date with the host mirror
 int flush_free(gt_ctx *c, bool all)
 {
     if (!c->n_nodes) return GT_OK;
     if (all || !c->free_uploaded) {
         GT_CUDA(c, cudaMemcpyAsync(c->d_free, c->h_free, (size_t)c->n_nodes * 2, cudaMemcpyHostToDevice, c->stream));
+        GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
+        c->h2d_pending = true;
         c->free_uploaded = true;
         return GT_OK;
     }
     const uint32_t n = (uint32_t)c->dirty.size();
     if (!n) return GT_OK;
+    int rcw = mirror_writable(c);   // the id / mask staging buffers are reused
+    if (rcw != GT_OK) return rcw;
     for (uint32_t i = 0; i < n; i++) {
         c->h_ids[i] = c->dirty[i];
         c->h_masks[i] = c->h_free[c->dirty[i]];
@@ -171,6 +187,8 @@ int flush_free(gt_ctx *c, bool all)
     k_scatter_free<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_ids, c->d_masks, n, c->d_free);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
+    GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
+    c->h2d_pending = true;
     return GT_OK;
 }
 
@@ -430,6 +448,7 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaHostAlloc(&c->h_masks, N * 2, cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_place, 16 * sizeof(unsigned long long), cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_row, 64, cudaHostAllocDefault));
+        GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_h2d, cudaEventDisableTiming));
         memset(c->h_free, 0, N * 2);
         memset(c->h_ngpus, 0, N);
         c->dirty_flag.assign(N, 0);
@@ -462,6 +481,7 @@ void gt_destroy(gt_ctx *c)
     for (auto &g : c->step_exec)
         if (g) cudaGraphExecDestroy(g);
     if (c->comm_stream) { cudaStreamSynchronize(c->comm_stream); cudaStreamDestroy(c->comm_stream); }
+    if (c->ev_h2d) cudaEventDestroy(c->ev_h2d);
     if (c->ev_pass) cudaEventDestroy(c->ev_pass);
     for (auto &e : c->ev_comm)
         if (e) cudaEventDestroy(e);
@@ -491,6 +511,10 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
     for (uint32_t i = 0; i < count; i++)
         if (n_gpus[i] > GT_MAX_GPUS) return fail(c, GT_ERR_INVALID, "gt_load_nodes: n_gpus > 16%s");
     GT_CUDA(c, cudaSetDevice(c->device));
+    {
+        int rcw = mirror_writable(c);
+        if (rcw != GT_OK) return rcw;
+    }
     GT_CUDA(c, cudaMemcpyAsync(c->d_levels + (size_t)first * 256, levels, (size_t)count * 256, cudaMemcpyHostToDevice, c->stream));
     memcpy(c->h_ngpus + first, n_gpus, count);
     memcpy(c->h_free + first, free_mask, (size_t)count * 2);
@@ -529,6 +553,9 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
 int gt_update_free(gt_ctx *c, const uint32_t *node_ids, const uint16_t *masks, uint32_t count)
 {
     if (!c || !masks) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    int rcw = mirror_writable(c);
+    if (rcw != GT_OK) return rcw;
     if (!node_ids) {
         if (count > c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_update_free: count exceeds loaded nodes%s");
         memcpy(c->h_free, masks, (size_t)count * 2);
@@ -557,6 +584,8 @@ int gt_commit(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t 
         if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_commit: node id out of range%s");
         if ((c->h_free[nodes[i]] & masks[i]) != masks[i]) return fail(c, GT_ERR_STATE, "gt_commit: GPU already in use%s");
     }
+    int rcw = mirror_writable(c);
+    if (rcw != GT_OK) return rcw;
     for (uint32_t i = 0; i < count; i++) {
         c->h_free[nodes[i]] &= (uint16_t)~masks[i];
         mark_dirty(c, nodes[i]);
@@ -569,6 +598,8 @@ int gt_release(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t
     if (!c || !nodes || !masks) return GT_ERR_INVALID;
     for (uint32_t i = 0; i < count; i++)
         if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_release: node id out of range%s");
+    int rcw = mirror_writable(c);
+    if (rcw != GT_OK) return rcw;
     for (uint32_t i = 0; i < count; i++) {
         c->h_free[nodes[i]] |= masks[i];
         mark_dirty(c, nodes[i]);
@@ -916,6 +947,7 @@ int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t
         return GT_OK;
     }
     // memo path: the GPU has scored every (class, free mask); the host loop only looks rows up
+    if ((rc = mirror_writable(c)) != GT_OK) return rc;
     const uint32_t N = c->n_nodes;
     MinTree tree;
     tree.init(std::max(N, 1u));
