@@ -341,3 +341,57 @@ def test_gaia_singular_policy_on_device(gt, oracle):
         # the commit loop keeps the policy too: a k = 1 pod on node 1 (cousin of GPU3 is used) takes GPU3 first
         placed, on, om = a.schedule(np.array([1], np.uint8), np.array([0], np.uint32))
         assert placed == 1 and int(on[0]) == 0 and int(om[0]) in (4, 8)
+
+
+def test_split_units_and_high_positions(gt, oracle):
+    """Shapes the work decomposition treats specially: many nodes with >= 14 free GPUs (a node spans several
+    warp units whose minima meet through atomics), 16-GPU nodes with <= 8 free GPUs at high indices, the maximum
+    cost table (255 everywhere: cost sums up to 120*255), and awkward node counts."""
+    rng = np.random.RandomState(21)
+    N = 3000
+    levels = rng.randint(1, 16, (N, 256)).astype(np.uint8)
+    n_gpus = np.full(N, 16, np.uint8)
+    free = np.zeros(N, np.uint16)
+    for i in range(N):
+        if i % 3 == 0:       # 14..16 free
+            m = 0xFFFF
+            for b in rng.choice(16, rng.randint(0, 3), replace=False):
+                m &= ~(1 << b)
+            free[i] = m
+        elif i % 3 == 1:     # <= 8 free, all in the upper half
+            free[i] = int(rng.randint(0, 256)) << 8
+        else:
+            free[i] = rng.randint(0, 1 << 16)
+    check_cluster(gt, oracle, levels, n_gpus, free, np.full(16, 255, np.uint8))
+    for n_nodes in (1, 31, 33, 127, 129, 257):
+        lv, n, fr, _ = gt.synth_cluster(4, 1000 + n_nodes, 0, n_nodes)
+        check_cluster(gt, oracle, lv, n, fr)
+
+
+def test_partial_loads_and_capacity(gt, oracle):
+    """Loading node ranges one after the other into a larger context equals loading them at once."""
+    lv, n, fr, _ = gt.synth_cluster(4, 31337, 0, 5000)
+    want, _ = oracle.exhaustive_cluster(lv, n, fr, oracle.lut(0), 8)
+    with gt.Allocator(8000) as a:
+        a.load_nodes(lv[:1234], n[:1234], fr[:1234], first=0)
+        a.load_nodes(lv[1234:], n[1234:], fr[1234:], first=1234)
+        assert a.num_nodes == 5000
+        assert (a.score_all() == want).all()
+        # reload a middle range with other free masks
+        fr2 = fr.copy()
+        fr2[2000:2100] = 0
+        a.load_nodes(lv[2000:2100], n[2000:2100], fr2[2000:2100], first=2000)
+        want2, _ = oracle.exhaustive_cluster(lv, n, fr2, oracle.lut(0), 8)
+        assert (a.score_all() == want2).all()
+        # whole-shard mask update
+        a.update_free(fr)
+        assert (a.score_all() == want).all()
+        # scattered mask update through the dirty path
+        ids = np.array([5, 4999, 2500], np.uint32)
+        a.update_free(np.zeros(3, np.uint16), node_ids=ids)
+        a.score_dirty()
+        fr3 = fr.copy()
+        fr3[ids] = 0
+        want3, _ = oracle.exhaustive_cluster(lv, n, fr3, oracle.lut(0), 8)
+        assert (a.score_all() == want3).all()
+        assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(want3)).all()
