@@ -299,10 +299,18 @@ def main():
         except Exception:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        traffic = None
+        try:   # dram__bytes_read.sum + dram__bytes_write.sum of one k_score launch, from the committed ncu capture
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            if tr.get("nodes") == N:
+                traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+        except Exception:
+            pass
         alg_bytes = N * (256 + 2 + 64)      # BASELINE.md section 5 with n = 16 storage: matrix + mask + best row
         roofline = {
             "kernel": "k_score (K1 + folded cluster argmin)", "bound": "alu", "achieved": alg_adds / t_score / 1e9, "peak": peak_adds / 1e9,
-            "unit": "Gadd/s", "frac": (alg_adds / t_score) / peak_adds, "traffic": None,
+            "unit": "Gadd/s", "frac": (alg_adds / t_score) / peak_adds, "traffic": traffic,
+            "traffic_note": "DRAM bytes of one k_score launch from profiles/r1_traffic.json (ncu); algorithmic bytes per launch = %d" % alg_bytes,
             "note": "ALU-bound path (BASELINE.md section 5): achieved = algorithmic pair-cost additions sum C(f,2)*2^(f-2) "
                     "per launch / kernel duration; peak = INT32 add rate measured live (k_int32_peak). The kernel does "
                     "fewer real instructions than the algorithmic count (incremental tree), so frac may exceed 1.",
