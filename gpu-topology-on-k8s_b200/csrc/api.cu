@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -84,6 +85,9 @@ struct gt_ctx {
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
     uint8_t *d_scores = nullptr;
+#ifdef GT_TRACE
+    unsigned long long *d_trace = nullptr;
+#endif
     // pinned host mirrors
     uint16_t *h_free = nullptr;
     uint8_t *h_ngpus = nullptr;
@@ -214,7 +218,10 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
     gt::ScoreParams p;
     p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
     p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
-    p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u;
+    p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
+#ifdef GT_TRACE
+    p.trace = c->d_trace;
+#endif
     return p;
 }
 
@@ -242,7 +249,8 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    static const bool no_pdl = getenv("GT_NO_PDL") != nullptr;   // profiling aid
+    cfg.numAttrs = no_pdl ? 0 : 1;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, score_params(c, fold, keep_bins)));
     c->launches++;
     if (fold) c->place_cur = fold;
@@ -332,7 +340,8 @@ int launch_argmin(gt_ctx *c)
     return GT_OK;
 }
 
-// Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1, one graph launch.
+// Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1, linked by programmatic
+// dependent launch (two plain launches; as a captured graph only with GT_FLAG_GRAPH).
 // Listed (dirty) nodes: K0 + K1 over the list, then K2 over the whole table.  n == 0: K2 only.
 int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
@@ -341,7 +350,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
     if (!d_ids && n) {
         bool done = false;
-        if (!(c->flags & GT_FLAG_NO_GRAPH) && !c->graph_failed) {
+        if ((c->flags & GT_FLAG_GRAPH) && !c->graph_failed) {   // measured slower than two plain launches: opt-in
             done = launch_step_graph(c, par) == GT_OK;
             if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
         }
@@ -436,6 +445,10 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
         GT_CUDA(c, cudaMalloc(&c->d_scores, N));
+#ifdef GT_TRACE
+        GT_CUDA(c, cudaMalloc(&c->d_trace, (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots * 8));
+        GT_CUDA(c, cudaMemset(c->d_trace, 0, (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots * 8));
+#endif
         GT_CUDA(c, cudaMemset(c->d_ngpus, 0, N));
         GT_CUDA(c, cudaMemset(c->d_free, 0, N * 2));
         GT_CUDA(c, cudaMemset(c->d_levels, 0, N * 256));
@@ -1146,10 +1159,27 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
                                                                      nullptr);
     gt::ScoreParams prm;
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
-    prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0;
+    prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;
+#ifdef GT_TRACE
+    return static_fail(GT_ERR_STATE, err_buf, err_len, "trace build: gt_score_nodes_static is disabled");
+#endif
     const uint32_t grid = std::min<uint32_t>(n_nodes / 8 + gt::kBins, (uint32_t)sms * gt::kScoreMinCtas);
     gt::k_score<<<grid, gt::kScoreCta, 0, s>>>(prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(GT_ERR_CUDA, err_buf, err_len, "kernel launch: ", cudaGetErrorString(e));
     return GT_OK;
 }
+
+#ifdef GT_TRACE
+// debug builds only: the per-warp event trace of the last k_score launch
+extern "C" int gt_debug_trace(gt_ctx *c, unsigned long long *out, uint32_t n_words)
+{
+    if (!c || !out) return GT_ERR_INVALID;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    const size_t have = (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots;
+    cudaMemcpy(out, c->d_trace, std::min<size_t>(have, n_words) * 8, cudaMemcpyDeviceToHost);
+    cudaMemset(c->d_trace, 0, have * 8);
+    return GT_OK;
+}
+#endif

@@ -33,6 +33,7 @@ constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
 constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the register budget is set for
 constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
 constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 16: shifts banks between tiles)
+constexpr int kStageBytes = kTilesPerWarp * kTileStride;   // staging buffer of a warp: 16 full tiles
 constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
 
 struct ScoreParams {
@@ -45,11 +46,50 @@ struct ScoreParams {
     uint32_t cap, first_node;
     uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
+    uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
+#ifdef GT_TRACE
+    unsigned long long *trace;   // [warps][kTraceSlots] (globaltimer ns << 8 | event id), debug builds only
+#endif
 };
+#ifdef GT_TRACE
+constexpr int kTraceSlots = 64;
+__device__ __forceinline__ unsigned long long gt_now()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define GT_TR(id)                                                                         \
+    do {                                                                                  \
+        if (lane == 0 && tr_n < kTraceSlots) tr[tr_n++] = (gt_now() << 8) | (unsigned)(id); \
+    } while (0)
+#else
+#define GT_TR(id) do { } while (0)
+#endif
 // scratch control block (u32 words): [0..16] bin counts, [17] K1 unit ticket, [18] K1 finished CTAs.
 // All zero between scoring passes: K1's last CTA clears it.
 constexpr int kCtlWords = 32;
 constexpr int kCtlTicket = 17, kCtlDone = 18;
+// K1 hands out work units bin by bin, costliest unit type first (measured per-unit times, profiles/): the
+// multi-node units of p = 9, 10 and the 32-node units of p = 8 are the long ones, tiny bins come last.
+// Kept as immediates (5 bits per entry), not in constant memory: a cold constant-cache miss in front of every
+// warp's first unit costs more than the whole decode.
+__host__ __device__ constexpr int bin_order_host(int i)
+{
+    constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+    return order[i];
+}
+__host__ __device__ constexpr unsigned long long bin_order_pack(int from, int to)
+{
+    unsigned long long v = 0;
+    for (int i = from; i < to; i++) v |= (unsigned long long)bin_order_host(i) << (5 * (i - from));
+    return v;
+}
+__device__ __forceinline__ int bin_order(int i)
+{
+    constexpr unsigned long long lo = bin_order_pack(0, 12), hi = bin_order_pack(12, kBins);
+    return (int)(((i < 12) ? (lo >> (5 * i)) : (hi >> (5 * (i - 12)))) & 31ull);
+}
 
 // ---------------------------------------------------------------- load time
 // cost[i][j] = cost[j][i] = lut[levels[min(i,j)][max(i,j)]], cost[i][i] = 0: the upper triangle of the level
@@ -89,9 +129,6 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
-    // programmatic dependent launch: K1 may be scheduled now; it waits (griddepcontrol.wait) for this
-    // grid to complete before it reads the bins
-    asm volatile("griddepcontrol.launch_dependents;");
     if (tid < kBins) s_cnt[tid] = 0;
     if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     __syncthreads();
@@ -119,6 +156,10 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
         bin_list[at] = node;
         bin_free[at] = (uint16_t)f;
     }
+    // programmatic dependent launch: from here on K1's CTAs may be scheduled while this grid drains; K1 waits
+    // (griddepcontrol.wait) for the whole grid before it reads the bins.  Triggering at the top of K0 instead
+    // was measured 3-6 us slower per pass: the waiting K1 CTAs crowd K0 off the SMs.
+    asm volatile("griddepcontrol.launch_dependents;");
 }
 
 // ---------------------------------------------------------------- the unrolled subset tree
@@ -152,9 +193,12 @@ struct Children {   // children of S add a position in [0, B)
     }
 };
 
-// ---------------------------------------------------------------- K1 small: one thread per node, p == P <= 8
-template <int P>
-__device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t node, uint32_t f, uint32_t (&out)[16])
+// ---------------------------------------------------------------- K1 small: one lane per node, p == P <= 8
+// tile: the node's cost tile -- in global memory (SMEM = false: the pair costs are gathered with independent
+// byte loads, one round trip; staging the tiles through shared memory first was measured slower, it adds a
+// second dependent stage in front of every unit) or staged in shared memory (SMEM = true, unused).
+template <int P, bool SMEM>
+__device__ __forceinline__ void score_small(const uint8_t *tile, uint32_t f, uint32_t (&out)[16])
 {
     if constexpr (P > 0) {
         uint32_t pos[P], bit[P];
@@ -165,13 +209,18 @@ __device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t nod
             pos[a] = (uint32_t)g;
             bit[a] = 1u << g;
         }
-        const uint8_t *cm = prm.cost + (size_t)node * 256;
         uint32_t c[P * P];
 #pragma unroll
         for (int a = 0; a < P; a++)
 #pragma unroll
-            for (int b = 0; b < P; b++)
-                c[a * P + b] = (a < b) ? ((uint32_t)__ldg(cm + pos[a] * 16 + pos[b]) << 16) : 0u;
+            for (int b = 0; b < P; b++) {
+                if (a < b) {
+                    const uint8_t v = SMEM ? tile[pos[a] * 16 + pos[b]] : __ldg(tile + pos[a] * 16 + pos[b]);
+                    c[a * P + b] = (uint32_t)v << 16;
+                } else {
+                    c[a * P + b] = 0u;
+                }
+            }
         uint32_t acc[P + 1], R[P];
 #pragma unroll
         for (int k = 0; k <= P; k++) acc[k] = kInf;
@@ -183,19 +232,42 @@ __device__ __forceinline__ void score_small(const ScoreParams &prm, uint32_t nod
     }
 }
 
-// lowest (cost, node) of a warp's candidates for request size k+1 -> one shared-memory atomicMin
-__device__ __forceinline__ void fold_place_warp(unsigned long long *s_place, int k, uint32_t v, uint32_t node,
-                                                uint32_t first_node)
+template <bool SMEM>
+__device__ __forceinline__ void score_small_any(int p, const uint8_t *tile, uint32_t f, uint32_t (&out)[16])
+{
+    switch (p) {
+    case 1: score_small<1, SMEM>(tile, f, out); break;
+    case 2: score_small<2, SMEM>(tile, f, out); break;
+    case 3: score_small<3, SMEM>(tile, f, out); break;
+    case 4: score_small<4, SMEM>(tile, f, out); break;
+    case 5: score_small<5, SMEM>(tile, f, out); break;
+    case 6: score_small<6, SMEM>(tile, f, out); break;
+    case 7: score_small<7, SMEM>(tile, f, out); break;
+    case 8: score_small<8, SMEM>(tile, f, out); break;
+    default: break;
+    }
+}
+
+// The cluster argmin is carried in registers: lane k (< 16) of every warp holds the warp's best
+// (value = cost<<16|mask, node) for request size k+1; it reaches shared / global memory once, at warp exit.
+struct WarpBest {
+    uint32_t v, node;
+    __device__ __forceinline__ void take(uint32_t nv, uint32_t nn)
+    {
+        if ((nv >> 16) < (v >> 16) || ((nv >> 16) == (v >> 16) && nn < node)) { v = nv; node = nn; }
+    }
+};
+
+// one lane per node: lowest (cost, node) of the warp's candidates for request size k+1 goes to lane k
+__device__ __forceinline__ void fold_small_warp(WarpBest &wb, int k, uint32_t v, uint32_t node, uint32_t lane)
 {
     const uint32_t cmin = __reduce_min_sync(0xFFFFFFFFu, v & 0xFFFF0000u);
     if (cmin != kInf) {   // warp-uniform
-        const uint32_t cand = ((v & 0xFFFF0000u) == cmin) ? node : 0xFFFFFFFFu;
-        const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, cand);
-        if (node == nmin && (v & 0xFFFF0000u) == cmin) {
-            const unsigned long long key = ((unsigned long long)(cmin >> 16) << 48) |
-                                           ((unsigned long long)(first_node + node) << 16) | (v & 0xFFFFu);
-            atomicMin(&s_place[k], key);
-        }
+        const bool tie = (v & 0xFFFF0000u) == cmin;
+        const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, tie ? node : 0xFFFFFFFFu);
+        const uint32_t owner = __ffs(__ballot_sync(0xFFFFFFFFu, tie && node == nmin)) - 1;
+        const uint32_t bv = __shfl_sync(0xFFFFFFFFu, v, (int)owner);
+        if (lane == (uint32_t)k) wb.take(bv, nmin);
     }
 }
 
@@ -262,14 +334,18 @@ __device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, i
 // Warp-private staging: the 16x16 cost tiles of the unit's nodes (coalesced 16-byte loads) and the
 // per-k minima of each node.  No CTA barrier in K1's work loop.
 struct WarpScratch {
-    __align__(16) uint8_t raw[kTilesPerWarp * kTileStride];
+    __align__(16) uint8_t raw[kStageBytes];
     uint32_t best[kTilesPerWarp][kBins];
 };
 
 // hb = p - 8 bits of H.  hb <= 5: a warp holds 32 >> hb nodes.  hb > 5: a node spans 2^(hb-5) warp units
 // whose minima meet in global memory (rows preset to kInf by k_bin).
-__device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScratch &ws, unsigned long long *s_place,
-                                               int p, uint32_t lu, uint32_t cnt, uint32_t lane)
+__device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScratch &ws, WarpBest &wb,
+                                               int p, uint32_t lu, uint32_t cnt, uint32_t lane
+#ifdef GT_TRACE
+                                               , unsigned long long *tr, int &tr_n
+#endif
+)
 {
     const int hb = p - 8;
     const uint32_t *list = prm.bin_list + (size_t)p * prm.cap;
@@ -290,6 +366,8 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     const bool active = slot < live;
     const uint32_t node = __ldg(list + first + (active ? slot : 0u));
     const uint32_t f = __ldg(flist + first + (active ? slot : 0u));
+    if (f == 0x12345u) GT_TR(99);
+    GT_TR(10);   // list entries arrived
     // stage tiles: 16 lanes x 16 B per tile, two tiles per pass
     for (uint32_t t = lane >> 4; t < live; t += 2) {
         const uint32_t nd = __ldg(list + first + t);
@@ -299,39 +377,29 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     for (uint32_t s2 = 0; s2 < live; s2++)
         if (lane < (uint32_t)kBins) ws.best[s2][lane] = kInf;
     __syncwarp();
+    GT_TR(11);   // tiles staged
     if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
     __syncwarp();
+    GT_TR(12);   // set-up + tree + atomics done
     if (hb <= 5) {
-        // lanes 0..15 of each half-warp write one row per pass: row of slot s2, k = (lane & 15) + 1
-        for (uint32_t s2 = lane >> 4; s2 < ((live + 1u) & ~1u); s2 += 2) {
-            const bool ok = s2 < live;
-            const uint32_t nd = __ldg(list + first + (ok ? s2 : 0u));
-            const uint32_t v = ok ? ws.best[s2][(lane & 15u) + 1u] : kInf;
-            if (ok) prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
-            if (prm.fold_place) {   // both half-warps hold candidates for k = (lane & 15) + 1
-                const uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, nd, 16);
-                const bool mine = (v >> 16) < (o >> 16) || ((v >> 16) == (o >> 16) && nd <= on);
-                if (lane < 16) {
-                    const uint32_t bv = mine ? v : o, bn = mine ? nd : on;
-                    if (bv != kInf) {
-                        const unsigned long long key = ((unsigned long long)(bv >> 16) << 48) |
-                            ((unsigned long long)(prm.first_node + bn) << 16) | (bv & 0xFFFFu);
-                        atomicMin(&s_place[lane], key);
-                    }
-                }
-            }
+        // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
+        WarpBest hb2;
+        hb2.v = kInf; hb2.node = 0xFFFFFFFFu;
+        for (uint32_t s2 = lane >> 4; s2 < live; s2 += 2) {
+            const uint32_t nd = __ldg(list + first + s2);
+            const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
+            prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+            hb2.take(v, nd);
         }
+        __syncwarp();
+        const uint32_t ov = __shfl_xor_sync(0xFFFFFFFFu, hb2.v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, hb2.node, 16);
+        hb2.take(ov, on);
+        if (lane < 16) wb.take(hb2.v, hb2.node);
     } else if (lane < 16) {
         const uint32_t v = ws.best[0][lane + 1];
         if (v != kInf) {
             atomicMin(prm.best + (size_t)node * 16 + lane, v);
-            if (prm.fold_place) {   // a partial minimum of the node is still a valid upper bound of its key... but
-                // only the node's true minimum may enter the argmin: fold partials -- the minimum over all of the
-                // node's warp units equals the node's row, and min is associative
-                const unsigned long long key = ((unsigned long long)(v >> 16) << 48) |
-                    ((unsigned long long)(prm.first_node + node) << 16) | (v & 0xFFFFu);
-                atomicMin(&s_place[lane], key);
-            }
+            wb.take(v, node);   // a partial minimum of a node is a real subset of it: folding it is exact
         }
     }
     __syncwarp();
@@ -346,64 +414,79 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 {
     __shared__ WarpScratch s_ws[kScoreCta / 32];
     __shared__ unsigned long long s_place[16];
-    __shared__ uint32_t s_cnt[kBins], s_end[kBins];   // s_end[i]: cumulative units after bin p = 16 - i
+    __shared__ uint32_t s_cnt[kBins], s_end[kBins];   // s_end[i]: cumulative units after bin bin_order(i)
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+#ifdef GT_TRACE
+    unsigned long long *tr = prm.trace + (size_t)(blockIdx.x * (kScoreCta / 32) + warp) * kTraceSlots;
+    int tr_n = 0;
+#endif
+    GT_TR(1);
     if (tid < 16) s_place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible (no-op without PDL)
-    if (tid < kBins) s_cnt[tid] = prm.ctl[tid];
-    __syncthreads();
-    if (tid == 0) {
-        uint32_t run = 0;
-        for (int i = 0; i < kBins; i++) {
-            const int p = 16 - i;
-            const uint32_t cnt = s_cnt[p];
-            if (p >= kSplitP) run += cnt << (p - 13);
-            else if (p > 8) run += (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
-            else run += (cnt + 31u) >> 5;
-            s_end[i] = run;
+    GT_TR(2);
+    // units per bin in hand-out order, then an inclusive scan inside warp 0 (17 lanes)
+    if (warp == 0) {
+        uint32_t units = 0, cnt = 0;
+        int p = 0;
+        if (lane < (uint32_t)kBins) {
+            p = bin_order((int)lane);
+            cnt = prm.ctl[p];
+            s_cnt[p] = cnt;
+            if (p >= kSplitP) units = cnt << (p - 13);
+            else if (p > 8) units = (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
+            else units = (cnt + 31u) >> 5;
         }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, units, d);
+            if (lane >= (uint32_t)d) units += o;
+        }
+        if (lane < (uint32_t)kBins) s_end[lane] = units;
     }
     __syncthreads();
     const uint32_t total = s_end[kBins - 1];
     WarpScratch &ws = s_ws[warp];
-    // first unit = this warp's global index; later ones come from the ticket, requested one unit ahead
-    // (plain PTX atom: the compiler's warp-aggregated atomicAdd would wait for the reply right away)
+    GT_TR(3);
+    // first unit = this warp's global index; later ones come from the ticket, requested one unit ahead.
+    // ptxas turns an atomic add on a provably warp-uniform address (even from inline PTX, even atom.inc) into
+    // a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once -- that stalled every
+    // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
     const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
     uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
     int i = 0;
+    WarpBest wb;
+    wb.v = kInf; wb.node = 0xFFFFFFFFu;
     while (u < total) {
         uint32_t next = 0;
         if (lane == 0)
-            asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket) : "memory");
-        next += n_warps;
+            asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket + prm.zero * tid) : "memory");
+        // `next` is not touched again before the end of this unit: the reply has a whole unit to arrive
         while (u >= s_end[i]) i++;            // units only grow: continue from the previous bin
-        const int p = 16 - i;
+        const int p = bin_order(i);
         const uint32_t lu = u - (i ? s_end[i - 1] : 0u);
         const uint32_t cnt = s_cnt[p];
+        GT_TR(32 + p);   // unit start
         if (p > 8) {
-            score_big_warp(prm, ws, s_place, p, lu, cnt, lane);
+#ifdef GT_TRACE
+            score_big_warp(prm, ws, wb, p, lu, cnt, lane, tr, tr_n);
+#else
+            score_big_warp(prm, ws, wb, p, lu, cnt, lane);
+#endif
         } else {
             const uint32_t idx = lu * 32u + lane;
             const bool ok = idx < cnt;
             uint32_t out[16];
 #pragma unroll
             for (int k = 0; k < 16; k++) out[k] = kInf;
-            uint32_t node = 0xFFFFFFFFu;
+            uint32_t node = 0xFFFFFFFFu, f = 0;
             if (ok) {
                 const size_t at = (size_t)p * prm.cap + idx;
                 node = __ldg(prm.bin_list + at);
-                const uint32_t f = __ldg(prm.bin_free + at);
-                switch (p) {
-                case 1: score_small<1>(prm, node, f, out); break;
-                case 2: score_small<2>(prm, node, f, out); break;
-                case 3: score_small<3>(prm, node, f, out); break;
-                case 4: score_small<4>(prm, node, f, out); break;
-                case 5: score_small<5>(prm, node, f, out); break;
-                case 6: score_small<6>(prm, node, f, out); break;
-                case 7: score_small<7>(prm, node, f, out); break;
-                case 8: score_small<8>(prm, node, f, out); break;
-                default: break;
-                }
+                f = __ldg(prm.bin_free + at);
+            }
+            if (ok) {
+                score_small_any<false>(p, prm.cost + (size_t)node * 256, f, out);
+                GT_TR(20);   // small: gathers + tree done
                 uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)node * 16);
                 o[0] = make_uint4(out[0], out[1], out[2], out[3]);
                 o[1] = make_uint4(out[4], out[5], out[6], out[7]);
@@ -413,12 +496,21 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             if (prm.fold_place) {
 #pragma unroll
                 for (int k = 0; k < 8; k++)
-                    if (k < p) fold_place_warp(s_place, k, out[k], node, prm.first_node);
+                    if (k < p) fold_small_warp(wb, k, out[k], node, lane);
             }
         }
-        u = __shfl_sync(0xFFFFFFFFu, next, 0);
+        GT_TR(13);   // written out / folded
+        u = __shfl_sync(0xFFFFFFFFu, next, 0) + n_warps;
+        GT_TR(14);   // next ticket known
     }
+    if (prm.fold_place && lane < 16 && wb.v != kInf) {
+        const unsigned long long key = ((unsigned long long)(wb.v >> 16) << 48) |
+                                       ((unsigned long long)(prm.first_node + wb.node) << 16) | (wb.v & 0xFFFFu);
+        atomicMin(&s_place[lane], key);
+    }
+    GT_TR(4);
     __syncthreads();
+    GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
     // the last CTA to finish leaves the control block zeroed for the next pass
     if (tid == 0) {

@@ -20,8 +20,8 @@ def all_masks_cluster(oracle, cls):
 def check_cluster(gt, oracle, levels, n_gpus, free, lut=None, threads=8):
     lut = oracle.lut(0) if lut is None else lut
     want, cnt = oracle.exhaustive_cluster(levels, n_gpus, free, lut, threads)
-    # plain launches (no CUDA graph) must give the same table and placement keys
-    with gt.Allocator(len(n_gpus), flags=gt.FLAG_NO_GRAPH) as a:
+    # the captured-graph variant of the pass must give the same table and placement keys
+    with gt.Allocator(len(n_gpus), flags=gt.FLAG_GRAPH) as a:
         a.set_cost_lut(lut)
         a.load_nodes(levels, n_gpus, free)
         assert (a.score_all() == want).all()

@@ -20,6 +20,6 @@ for config in configs:
         with gt.Allocator(n) as a:
             a.load_nodes(lv, ng, fr)
             subsets, adds = a.count_subsets()
-            t = {k: a.time_kernel(k, 30) * 1e3 for k in ("step", "bin", "score")}
-            print("config %2d N %7d subsets %11d  step %8.2f us  bin %7.2f  score %8.2f   %.3e subsets/s" % (
-                config, n, subsets, t["step"], t["bin"], t["score"], subsets / (t["step"] * 1e-6)))
+            t = {k: a.time_kernel(k, 30) * 1e3 for k in ("step", "step_nograph", "bin", "score")}
+            print("config %2d N %7d subsets %11d  step %8.2f us (no graph %6.2f)  bin %7.2f  score %8.2f   %.3e subsets/s" % (
+                config, n, subsets, t["step"], t["step_nograph"], t["bin"], t["score"], subsets / (t["step"] * 1e-6)))
