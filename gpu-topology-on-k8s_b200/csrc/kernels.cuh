@@ -258,17 +258,29 @@ struct WarpBest {
     }
 };
 
-// one lane per node: lowest (cost, node) of the warp's candidates for request size k+1 goes to lane k
-__device__ __forceinline__ void fold_small_warp(WarpBest &wb, int k, uint32_t v, uint32_t node, uint32_t lane)
+// One lane per node: the lowest (cost, node) of the warp's candidates for request sizes K0+1 .. K0+4 goes to
+// lanes K0 .. K0+3.  Straight-line on purpose: the four reductions of each stage are independent, so their
+// latencies overlap (a branchy per-k version measured ~250 ns per k).  Rows beyond p hold kInf and fold to a no-op.
+template <int K0>
+__device__ __forceinline__ void fold_small_warp4(WarpBest &wb, const uint32_t (&out)[16], uint32_t node, uint32_t lane)
 {
-    const uint32_t cmin = __reduce_min_sync(0xFFFFFFFFu, v & 0xFFFF0000u);
-    if (cmin != kInf) {   // warp-uniform
-        const bool tie = (v & 0xFFFF0000u) == cmin;
-        const uint32_t nmin = __reduce_min_sync(0xFFFFFFFFu, tie ? node : 0xFFFFFFFFu);
-        const uint32_t owner = __ffs(__ballot_sync(0xFFFFFFFFu, tie && node == nmin)) - 1;
-        const uint32_t bv = __shfl_sync(0xFFFFFFFFu, v, (int)owner);
-        if (lane == (uint32_t)k) wb.take(bv, nmin);
+    uint32_t cmin[4], nmin[4], bv[4];
+    bool tie[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) cmin[q] = __reduce_min_sync(0xFFFFFFFFu, out[K0 + q] & 0xFFFF0000u);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        tie[q] = (out[K0 + q] & 0xFFFF0000u) == cmin[q];
+        nmin[q] = __reduce_min_sync(0xFFFFFFFFu, tie[q] ? node : 0xFFFFFFFFu);
     }
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint32_t owner = __ffs(__ballot_sync(0xFFFFFFFFu, tie[q] && node == nmin[q])) - 1;
+        bv[q] = __shfl_sync(0xFFFFFFFFu, out[K0 + q], (int)(owner & 31u));
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        if (lane == (uint32_t)(K0 + q) && cmin[q] != kInf) wb.take(bv[q], nmin[q]);
 }
 
 // ---------------------------------------------------------------- K1 big: p > 8, 2^(p-8) lanes per node
@@ -494,9 +506,8 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 o[3] = make_uint4(kInf, kInf, kInf, kInf);
             }
             if (prm.fold_place) {
-#pragma unroll
-                for (int k = 0; k < 8; k++)
-                    if (k < p) fold_small_warp(wb, k, out[k], node, lane);
+                fold_small_warp4<0>(wb, out, node, lane);
+                if (p > 4) fold_small_warp4<4>(wb, out, node, lane);
             }
         }
         GT_TR(13);   // written out / folded

@@ -55,8 +55,9 @@ for w in np.nonzero(used)[0]:
             end = sub.get(14, sub.get(13, start))
             rec = [sub.get(10, start) - start, sub.get(11, start) - sub.get(10, start), sub.get(12, start) - sub.get(11, start),
                    sub.get(13, start) - sub.get(12, sub.get(20, start)), sub.get(14, start) - sub.get(13, start), end - start]
-            if p <= 8:
-                rec = [0, 0, sub.get(20, start) - start, sub.get(13, start) - sub.get(20, start), sub.get(14, start) - sub.get(13, start), end - start]
+            if p <= 8:   # columns reused: gathers-wait, tree
+                rec = [sub.get(21, start) - start, sub.get(20, start) - sub.get(21, start), sub.get(22, start) - sub.get(20, start),
+                       sub.get(13, start) - sub.get(22, start), sub.get(14, start) - sub.get(13, start), end - start]
             unit_dur[p].append(rec)
             cnt += 1
             i = j
@@ -90,7 +91,7 @@ for k in (1, 2, 3, 4, 5):
     v = np.array(phase[k])
     print("%-22s min %7d  median %7d  max %7d ns" % (names[k], v.min(), np.median(v), v.max()))
 print("units per warp: mean %.2f max %d" % (np.mean(units_per_warp), max(units_per_warp)))
-print("per-unit ns (median): p  count | list-wait  stage  setup+tree  writeout  ticket-wait | total")
+print("per-unit ns (median): p  count | list-wait  stage  setup+tree  writeout  ticket-wait | total   (p <= 8: gathers-wait, tree, row stores, fold)")
 for p in sorted(unit_dur, reverse=True):
     r = np.array(unit_dur[p])
     med = np.median(r, axis=0)
