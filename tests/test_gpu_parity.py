@@ -395,3 +395,23 @@ def test_partial_loads_and_capacity(gt, oracle):
         want3, _ = oracle.exhaustive_cluster(lv, n, fr3, oracle.lut(0), 8)
         assert (a.score_all() == want3).all()
         assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(want3)).all()
+
+
+def test_gpu_matches_committed_golden_sweep(gt, oracle):
+    """The CUDA path against the committed vectors of tests/golden/sweep_small.npz (no oracle call involved)."""
+    import os
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "sweep_small.npz"))
+    for name in ("DGX1", "F1_RING", "F2_PCIE", "F3_TREE4"):
+        lv, n, _, _ = oracle.class_topology(ol.CLS[name])
+        N = 1 << n
+        with gt.Allocator(N) as a:
+            a.load_nodes(np.tile(lv, (N, 1)), np.full(N, n, np.uint8), np.arange(N, dtype=np.uint16))
+            for preset in (0, 1):
+                a.set_cost_lut(gt.lut_preset(preset))
+                assert (a.score_all() == gold["%s_lut%d" % (name, preset)]).all()
+    lv, n, fr, _ = gt.synth_cluster(2, 0x5EED0002, 0, 1000)
+    assert (fr == gold["config2_free"]).all()
+    with gt.Allocator(1000) as a:
+        a.load_nodes(lv, n, fr)
+        a.score_all(fetch=False)
+        assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == gold["config2_place"]).all()

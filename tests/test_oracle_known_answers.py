@@ -258,3 +258,16 @@ def test_replay_sequential_semantics(oracle):
             live.append((nd, m))
             assert (int(on[e]), int(om[e])) == (nd, m)
     assert (free == fr_after).all()
+
+
+def test_oracle_matches_committed_golden_sweep(oracle):
+    """tests/golden/sweep_small.npz (made by tests/golden/make_golden.py) pins the oracle's output."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(GOLD, "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    want = np.load(os.path.join(GOLD, "sweep_small.npz"))
+    got = mg.build()
+    assert sorted(got) == sorted(want.files)
+    for k in want.files:
+        assert (got[k] == want[k]).all(), k
