@@ -84,7 +84,9 @@ struct gt_ctx {
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
-    uint8_t *d_scores = nullptr;
+    uint8_t *h_scores = nullptr;                // mapped pinned: k_sort_scores writes the reply straight to the host
+    uint32_t *d_scores_map = nullptr;           // device view of h_scores
+    unsigned long long *h_place_map = nullptr, *d_place_map = nullptr;   // same for the 16 placement keys
 #ifdef GT_TRACE
     unsigned long long *d_trace = nullptr;
 #endif
@@ -444,7 +446,10 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
-        GT_CUDA(c, cudaMalloc(&c->d_scores, N));
+        GT_CUDA(c, cudaHostAlloc(&c->h_scores, (N + 3) / 4 * 4, cudaHostAllocMapped));
+        GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_scores_map, c->h_scores, 0));
+        GT_CUDA(c, cudaHostAlloc(&c->h_place_map, 16 * sizeof(unsigned long long), cudaHostAllocMapped));
+        GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_place_map, c->h_place_map, 0));
 #ifdef GT_TRACE
         GT_CUDA(c, cudaMalloc(&c->d_trace, (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots * 8));
         GT_CUDA(c, cudaMemset(c->d_trace, 0, (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots * 8));
@@ -488,7 +493,7 @@ void gt_destroy(gt_ctx *c)
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_place);
-    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_scores);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     for (auto &g : c->step_exec)
@@ -1018,17 +1023,16 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     if (!c->n_nodes) return GT_OK;
     uint32_t cmax = 0;
     for (int i = 1; i < 16; i++) cmax = std::max<uint32_t>(cmax, c->lut[i]);
-    gt::k_sort_scores<<<(c->n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, m, cmax,
-                                                                                         c->d_scores);
+    if (out_place && c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
+    // the kernel stores scores and keys into mapped pinned memory: no device-to-host copy behind it
+    const uint32_t threads = (c->n_nodes + 3) / 4;
+    gt::k_sort_scores<<<(std::max(threads, 16u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+        c->d_best, c->n_nodes, m, cmax, c->d_scores_map, c->place_cur, out_place ? c->d_place_map : nullptr);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
-    GT_CUDA(c, cudaMemcpyAsync(out_scores, c->d_scores, c->n_nodes, cudaMemcpyDeviceToHost, c->stream));
-    if (out_place) {   // the host choice for every request size rides on the same synchronisation
-        if (c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
-        GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-    }
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (out_place) memcpy(out_place, c->h_place, 16 * sizeof(uint64_t));
+    memcpy(out_scores, c->h_scores, c->n_nodes);
+    if (out_place) memcpy(out_place, c->h_place_map, 16 * sizeof(uint64_t));
     return GT_OK;
 }
 

@@ -645,18 +645,32 @@ __global__ void __launch_bounds__(kCta) k_singular(const uint8_t *__restrict__ n
 
 // ---------------------------------------------------------------- "sort" verb: HostPriority scores 0..10
 // score = floor(10 * (cmax*len - cost) / (cmax*len)), len = C(m,2) (design.md:205-217); infeasible -> 0
+// Four nodes per thread, one 4-byte store: `scores` (and `out_place`) may be mapped pinned host memory, so the
+// reply goes straight over PCIe in 128-byte warp stores and needs no separate device-to-host copy.
 __global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict__ best, uint32_t n, uint32_t m,
-                                                      uint32_t cmax, uint8_t *__restrict__ scores)
+                                                      uint32_t cmax, uint32_t *__restrict__ scores4,
+                                                      const unsigned long long *__restrict__ place,
+                                                      unsigned long long *__restrict__ out_place)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t b = best[(size_t)i * 16 + (m - 1)];
-    uint32_t sc = 0;
-    if (b != kInf) {
-        const uint32_t den = cmax * (m * (m - 1) / 2), cost = b >> 16;
-        sc = den == 0 ? 10u : (cost >= den ? 0u : (10u * (den - cost)) / den);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (out_place && t < 16) out_place[t] = place[t];
+    const uint32_t i0 = t * 4;
+    if (i0 >= n) return;
+    const uint32_t den = cmax * (m * (m - 1) / 2);
+    uint32_t packed = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t sc = 0;
+        if (i0 + q < n) {
+            const uint32_t b = best[(size_t)(i0 + q) * 16 + (m - 1)];
+            if (b != kInf) {
+                const uint32_t cost = b >> 16;
+                sc = den == 0 ? 10u : (cost >= den ? 0u : (10u * (den - cost)) / den);
+            }
+        }
+        packed |= sc << (8 * q);
     }
-    scores[i] = (uint8_t)sc;
+    scores4[t] = packed;
 }
 
 // launch-cadence probes for profiling (no work)
