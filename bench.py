@@ -287,6 +287,14 @@ def main():
         c = ctxs[0]
         for name in ("step", "step_nograph", "bin", "score", "argmin"):
             kernels[name + "_us"] = c.time_kernel(name, 50) * 1e3
+        # not the measured path: what a pass costs when the rows come out of the GPU-built (class, free mask)
+        # table instead of being enumerated again (GT_FLAG_MEMO_PASS; SURVEY.md section 7 asks not to hide it)
+        lv0, n0, fr0, _ = gt.synth_cluster(4, SEED, first, N)
+        with gt.Allocator(N, device=local_rank, first_node=first, flags=gt.FLAG_MEMO_PASS) as am:
+            am.load_nodes(lv0, n0, fr0)
+            am.score_all(fetch=False)
+            kernels["memo_pass_us"] = am.time_kernel("step", 50) * 1e3
+        del lv0
         peak_ms = c.time_kernel("int32_peak", 5)
         sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
         peak_adds = sms * 8 * 256 * 2048 * 128 / (peak_ms * 1e-3)

@@ -114,6 +114,12 @@ struct gt_ctx {
     std::vector<size_t> memo_off;          // first row of each class
     uint32_t memo_classes = 0;             // classes covered by `memo`
     uint64_t lut_version = 0, memo_lut_version = ~0ull;
+    // GT_FLAG_MEMO_PASS: the same table on the device, plus each node's class and each class's first row
+    uint32_t *d_memo = nullptr, *d_row0 = nullptr, *d_node_class = nullptr;
+    uint32_t dmemo_classes = 0;
+    uint64_t dmemo_lut_version = ~0ull;
+    bool classes_uploaded = false;
+    bool memo_pass_failed = false;
     char err[256];
 };
 
@@ -342,6 +348,44 @@ int launch_argmin(gt_ctx *c)
     return GT_OK;
 }
 
+extern "C" {
+int build_memo(gt_ctx *c);   // defined with gt_schedule (inside the extern "C" block: same linkage here)
+}
+
+// GT_FLAG_MEMO_PASS: one row copy per node out of the GPU-built (class, free mask) table
+int launch_memo_pass(gt_ctx *c, unsigned long long *place)
+{
+    int rc = build_memo(c);            // K0 + K1 over every (class, mask); GT_ERR_RANGE when there are too many classes
+    if (rc != GT_OK) return rc;
+    const uint32_t ncls = (uint32_t)c->class_tile.size();
+    if (c->dmemo_classes != ncls || c->dmemo_lut_version != c->lut_version) {
+        cudaFree(c->d_memo); cudaFree(c->d_row0);
+        c->d_memo = c->d_row0 = nullptr;
+        std::vector<uint32_t> row0(ncls);
+        for (uint32_t k = 0; k < ncls; k++) row0[k] = (uint32_t)c->memo_off[k];
+        GT_CUDA(c, cudaMalloc(&c->d_memo, c->memo.size() * 4));
+        GT_CUDA(c, cudaMalloc(&c->d_row0, (size_t)ncls * 4));
+        GT_CUDA(c, cudaMemcpy(c->d_memo, c->memo.data(), c->memo.size() * 4, cudaMemcpyHostToDevice));
+        GT_CUDA(c, cudaMemcpy(c->d_row0, row0.data(), (size_t)ncls * 4, cudaMemcpyHostToDevice));
+        c->dmemo_classes = ncls;
+        c->dmemo_lut_version = c->lut_version;
+    }
+    if (!c->classes_uploaded) {
+        if (!c->d_node_class) GT_CUDA(c, cudaMalloc(&c->d_node_class, (size_t)c->cap * 4));
+        GT_CUDA(c, cudaMemcpy(c->d_node_class, c->node_class.data(), (size_t)c->n_nodes * 4, cudaMemcpyHostToDevice));
+        c->classes_uploaded = true;
+    }
+    GT_CUDA(c, cudaMemsetAsync(place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
+    const size_t quarters = (size_t)c->n_nodes * 4;
+    const uint32_t grid = (uint32_t)std::min<size_t>((quarters + gt::kCta * 4 - 1) / (gt::kCta * 4), (size_t)c->num_sms * 8);
+    gt::k_memo_pass<<<std::max(grid, 1u), gt::kCta, 0, c->stream>>>(c->d_memo, c->d_row0, c->d_node_class, c->d_ngpus,
+                                                                   c->d_free, c->n_nodes, c->first_node, c->d_best, place);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    c->place_cur = place;
+    return GT_OK;
+}
+
 // Full pass (d_ids == nullptr): K0 + K1 with the cluster argmin folded into K1, linked by programmatic
 // dependent launch (two plain launches; as a captured graph only with GT_FLAG_GRAPH).
 // Listed (dirty) nodes: K0 + K1 over the list, then K2 over the whole table.  n == 0: K2 only.
@@ -352,7 +396,13 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
     if (!d_ids && n) {
         bool done = false;
-        if ((c->flags & GT_FLAG_GRAPH) && !c->graph_failed) {   // measured slower than two plain launches: opt-in
+        if ((c->flags & GT_FLAG_MEMO_PASS) && !c->memo_pass_failed) {
+            rc = launch_memo_pass(c, bin_place(c, par));
+            if (rc == GT_ERR_RANGE) c->memo_pass_failed = true;   // too many topology classes: enumerate as usual
+            else if (rc != GT_OK) return rc;
+            else done = true;
+        }
+        if (!done && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed) {   // measured slower than two plain launches: opt-in
             done = launch_step_graph(c, par) == GT_OK;
             if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
         }
@@ -492,7 +542,7 @@ void gt_destroy(gt_ctx *c)
         if (api) api->CommDestroy(c->comm);
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
-    cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_place);
+    cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_memo); cudaFree(c->d_row0); cudaFree(c->d_node_class); cudaFree(c->d_place);
     cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
@@ -553,6 +603,7 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
             }
             c->node_class[first + i] = it->second;
         }
+        c->classes_uploaded = false;
     }
     GT_CUDA(c, cudaMemcpyAsync(c->d_ngpus + first, c->h_ngpus + first, count, cudaMemcpyHostToDevice, c->stream));
     GT_CUDA(c, cudaMemcpyAsync(c->d_free + first, c->h_free + first, (size_t)count * 2, cudaMemcpyHostToDevice, c->stream));

@@ -583,6 +583,56 @@ __global__ void __launch_bounds__(kCta) k_argmin(const uint32_t *__restrict__ be
     if (tid < 16 && s_min[tid] != ~0ull) atomicMin(&place[tid], s_min[tid]);
 }
 
+// ---------------------------------------------------------------- memo pass (GT_FLAG_MEMO_PASS)
+// The best row of a node depends only on (topology class, free mask): with few classes the GPU scores every
+// (class, mask) once (K0 + K1 over a pseudo-cluster) and a pass becomes one row copy per node plus the cluster
+// argmin.  Same thread layout as k_argmin: a thread moves 16-byte quarters of rows, so its four k are fixed.
+__global__ void __launch_bounds__(kCta) k_memo_pass(const uint32_t *__restrict__ memo, const uint32_t *__restrict__ row0,
+                                                    const uint32_t *__restrict__ node_class,
+                                                    const uint8_t *__restrict__ n_gpus,
+                                                    const uint16_t *__restrict__ free_mask, uint32_t n,
+                                                    uint32_t first_node, uint32_t *__restrict__ best,
+                                                    unsigned long long *__restrict__ place)
+{
+    __shared__ unsigned long long s_min[16];
+    const uint32_t tid = threadIdx.x;
+    if (tid < 16) s_min[tid] = ~0ull;
+    __syncthreads();
+    unsigned long long m[4] = {~0ull, ~0ull, ~0ull, ~0ull};
+    const size_t total = (size_t)n * 4;
+    const size_t stride = (size_t)gridDim.x * kCta;
+    for (size_t e = (size_t)blockIdx.x * kCta + tid; e < total; e += stride) {
+        const uint32_t node = (uint32_t)(e >> 2), q = (uint32_t)(e & 3);
+        uint32_t ng = n_gpus[node];
+        ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
+        const uint32_t f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(memo + ((size_t)row0[node_class[node]] + f) * 16) + q);
+        reinterpret_cast<uint4 *>(best)[e] = v;
+        const unsigned long long nd = ((unsigned long long)(first_node + node)) << 16;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned long long key = ((unsigned long long)(w[j] >> 16) << 48) | nd | (w[j] & 0xFFFFu);
+            if (w[j] != kInf && key < m[j]) m[j] = key;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+#pragma unroll
+        for (int sh = 16; sh >= 4; sh >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, m[j], sh);
+            m[j] = o < m[j] ? o : m[j];
+        }
+    }
+    if ((tid & 31u) < 4u) {
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if (m[j] != ~0ull) atomicMin(&s_min[(tid & 3u) * 4 + j], m[j]);
+    }
+    __syncthreads();
+    if (tid < 16 && s_min[tid] != ~0ull) atomicMin(&place[tid], s_min[tid]);
+}
+
 // ---------------------------------------------------------------- INT32 add peak (roofline denominator)
 // 8 independent IADD chains per thread; ops = grid*block*iters*8*unroll
 __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t iters, uint32_t seed)

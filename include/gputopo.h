@@ -57,7 +57,9 @@ enum {
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
 enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
 enum { GT_FLAG_GRAPH = 2 /* replay K0 -> K1 as a captured CUDA graph instead of two plain launches (measured slower) */,
-       GT_FLAG_NO_MEMO = 4 /* gt_schedule re-scores on the GPU per event instead of using the memo table */ };
+       GT_FLAG_NO_MEMO = 4 /* gt_schedule re-scores on the GPU per event instead of using the memo table */,
+       GT_FLAG_MEMO_PASS = 8 /* full passes copy rows out of the GPU-built (topology class, free mask) table instead of
+                                enumerating again; falls back to enumeration when there are too many classes */ };
 
 typedef struct gt_ctx gt_ctx;
 

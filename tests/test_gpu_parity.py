@@ -26,6 +26,14 @@ def check_cluster(gt, oracle, levels, n_gpus, free, lut=None, threads=8):
         a.load_nodes(levels, n_gpus, free)
         assert (a.score_all() == want).all()
         assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(want)).all()
+    # rows copied out of the GPU-built (class, free mask) table (falls back to enumeration with many classes)
+    with gt.Allocator(len(n_gpus), flags=gt.FLAG_MEMO_PASS) as a:
+        a.set_cost_lut(lut)
+        a.load_nodes(levels, n_gpus, free)
+        assert (a.score_all() == want).all()
+        assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == oracle.cluster_argmin(want)).all()
+        a.update_free(np.zeros(len(n_gpus), np.uint16))
+        assert (a.score_all() == ol.INFEASIBLE).all()
     with gt.Allocator(len(n_gpus)) as a:
         a.set_cost_lut(lut)
         a.load_nodes(levels, n_gpus, free)

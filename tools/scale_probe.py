@@ -21,5 +21,9 @@ for config in configs:
             a.load_nodes(lv, ng, fr)
             subsets, adds = a.count_subsets()
             t = {k: a.time_kernel(k, 30) * 1e3 for k in ("step", "step_nograph", "bin", "score")}
-            print("config %2d N %7d subsets %11d  step %8.2f us (no graph %6.2f)  bin %7.2f  score %8.2f   %.3e subsets/s" % (
-                config, n, subsets, t["step"], t["step_nograph"], t["bin"], t["score"], subsets / (t["step"] * 1e-6)))
+            with gt.Allocator(n, flags=gt.FLAG_MEMO_PASS) as am:
+                am.load_nodes(lv, ng, fr)
+                am.score_all(fetch=False)
+                t["memo"] = am.time_kernel("step", 30) * 1e3
+            print("config %2d N %7d subsets %11d  step %8.2f us (no graph %6.2f)  bin %7.2f  score %8.2f  memo-pass %6.2f   %.3e subsets/s" % (
+                config, n, subsets, t["step"], t["step_nograph"], t["bin"], t["score"], t["memo"], subsets / (t["step"] * 1e-6)))
