@@ -334,10 +334,24 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         oracle = load_oracle()
         sample = args.cpu_sample_nodes or min(N, 100000)
-        cnt, dt1 = cpu_sample(gt, oracle, sample, 1)
         cores = os.cpu_count() or 1
+        cnt, dt1 = cpu_sample(gt, oracle, sample, 1)
         cntm, dtm = cpu_sample(gt, oracle, sample, cores, repeats=3)
+        # the reference design's own greedy (design.md:153-186) on the same nodes, every m per node: it answers
+        # the same questions without scoring every subset, so its rate is given in (node, m) decisions per second
+        lvg, ng_, frg, _ = gt.synth_cluster(4, SEED, 0, sample)
+        t0 = time.perf_counter()
+        gbest, gdec = oracle.greedy_cluster(lvg, ng_, frg, oracle.lut(0))
+        gdt = time.perf_counter() - t0
+        xbest, _ = oracle.exhaustive_cluster(lvg, ng_, frg, oracle.lut(0), cores)
+        feas = xbest != 0xFFFF0000
+        worse = int(((gbest >> 16) > (xbest >> 16))[feas].sum())
+        del lvg
         cpu_baseline = {"value": cnt / dt1, "unit": UNIT, "cores": 1, "kind": "port",
+                        "greedy_design_md": {"decisions_per_s": gdec / gdt, "cores": 1, "decisions": gdec,
+                                             "costlier_than_optimum": worse,
+                                             "note": "node x request-size decisions/s of the literal design.md heuristic; "
+                                                     "`costlier_than_optimum` of them pick a strictly costlier GPU set than the exhaustive path"},
                         "sample": "first %d nodes of the config-4 cluster (%d subsets), oracle/gt_oracle.c -O2" % (sample, cnt),
                         "all_cores": {"value": cntm / dtm, "cores": cores}}
 

@@ -179,6 +179,24 @@ uint16_t gto_greedy_node(const uint8_t levels[256], int n_gpus, uint16_t free_ma
     return (uint16_t)ids;
 }
 
+uint64_t gto_greedy_cluster(const uint8_t *levels, const uint8_t *n_gpus, const uint16_t *free_mask,
+                            uint32_t n_nodes, const uint8_t lut[16], uint32_t *out_best)
+{
+    uint32_t i; uint64_t decisions = 0;
+    for (i = 0; i < n_nodes; i++) {
+        int n = n_gpus[i] > GTO_MAX_GPUS ? GTO_MAX_GPUS : n_gpus[i], m, p;
+        uint32_t f = n ? (free_mask[i] & ((1u << n) - 1u)) : 0;
+        for (m = 0; m < 16; m++) out_best[(size_t)i * 16 + m] = GTO_INFEASIBLE;
+        p = __builtin_popcount(f);
+        for (m = 1; m <= p; m++) {
+            uint32_t cost; uint16_t mask = gto_greedy_node(levels + (size_t)i * 256, n, (uint16_t)f, lut, m, &cost);
+            out_best[(size_t)i * 16 + m - 1] = (cost << 16) | mask;
+            decisions++;
+        }
+    }
+    return decisions;
+}
+
 /* ------------------------------------------------------------------ Gaia Alg. 3 / 4 / 1 */
 
 /* gpu_scheduler_algorithm_1.png lines 1-10 */

@@ -66,6 +66,12 @@ void gto_cluster_argmin(const uint32_t *best, uint32_t n_nodes, uint32_t first_n
 uint16_t gto_greedy_node(const uint8_t levels[256], int n_gpus, uint16_t free_mask,
                          const uint8_t lut[16], int m, uint32_t *out_cost);
 
+/* The reference design's own heuristic over a cluster: for every node and every m = 1..popcount(free) the greedy
+ * choice (timed as the "what the reference would have run" CPU baseline).  out_best as gto_exhaustive_cluster.
+ * Returns the number of (node, m) decisions made. */
+uint64_t gto_greedy_cluster(const uint8_t *levels, const uint8_t *n_gpus, const uint16_t *free_mask,
+                            uint32_t n_nodes, const uint8_t lut[16], uint32_t *out_best);
+
 /* Gaia Alg. 3 Singular (m == 1): candidates = free GPU whose siblings ("cousin") are all used
  * (and that has at least one sibling); lowest access cost, then lowest id; if none, the free GPU
  * with lowest access cost.  Returns gpu id or -1. */

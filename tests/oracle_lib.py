@@ -37,6 +37,7 @@ class Oracle:
         L.gto_exhaustive_node.restype = C.c_uint64
         L.gto_exhaustive_cluster.restype = C.c_uint64
         L.gto_greedy_node.restype = C.c_uint16
+        L.gto_greedy_cluster.restype = C.c_uint64
         L.gto_gaia_singular.restype = C.c_int
         L.gto_gaia_link.restype = C.c_uint16
         L.gto_gaia_dispatch.restype = C.c_uint16
@@ -71,6 +72,13 @@ class Oracle:
         out = np.zeros((N, 16), np.uint32)
         cnt = self.lib.gto_exhaustive_cluster(_p(levels, u8p), _p(n_gpus, u8p), _p(free, u16p), C.c_uint32(N),
                                               _p(lut, u8p), _p(out, u32p), C.c_int(threads))
+        return out, int(cnt)
+
+    def greedy_cluster(self, levels, n_gpus, free, lut):
+        N = len(n_gpus)
+        out = np.zeros((N, 16), np.uint32)
+        cnt = self.lib.gto_greedy_cluster(_p(levels, u8p), _p(n_gpus, u8p), _p(free, u16p), C.c_uint32(N), _p(lut, u8p),
+                                          _p(out, u32p))
         return out, int(cnt)
 
     def cluster_argmin(self, best, first=0):

@@ -188,6 +188,20 @@ def test_greedy_never_beats_exhaustive_and_diverges_on_f1(oracle):
     assert worse["F1_RING"] > 0 and worse["DGX1"] > 0
 
 
+def test_greedy_cluster_is_the_per_node_greedy(oracle):
+    """The cluster form timed by bench.py's cpu_baseline is the per-node greedy for every m, INF rows above popcount."""
+    lut = oracle.lut(0)
+    lv, n, fr, _ = oracle.synth_cluster(4, 77, 0, 300)
+    out, cnt = oracle.greedy_cluster(lv, n, fr, lut)
+    assert cnt == sum(bin(int(f) & ((1 << int(g)) - 1)).count("1") for f, g in zip(fr, n))
+    for i in range(300):
+        p = bin(int(fr[i]) & ((1 << int(n[i])) - 1)).count("1")
+        assert (out[i, p:] == ol.INFEASIBLE).all()
+        for m in range(1, p + 1):
+            g, gc = oracle.greedy_node(lv[i], int(n[i]), int(fr[i]), lut, m)
+            assert int(out[i, m - 1]) == (gc << 16) | g
+
+
 def test_gaia_link_matches_exhaustive_on_trees(oracle):
     """Cross-check: on tree-shaped topologies with all GPUs free Alg. 4 is cost-optimal."""
     lut = oracle.lut(0)
