@@ -28,6 +28,7 @@ EXPORTS = [
     "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static", "gt_schedule", "gt_synth_events",
     "gt_parse_topo_matrix", "gt_annotation_encode", "gt_annotation_decode", "gt_group_encode", "gt_group_decode",
     "gt_bind_annotations", "gt_ext_sort", "gt_ext_bind", "gt_plugin_allocate",
+    "gt_tree_tables", "gt_load_trees", "gt_gaia_select",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -41,6 +42,47 @@ class GtConfig(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("max_nodes", C.c_uint32),
                 ("first_node", C.c_uint32), ("k1_policy", C.c_uint32), ("flags", C.c_uint32),
                 ("stream", C.c_void_p)]
+
+
+class GtTree(C.Structure):
+    """Gaia resource-access cost tree (include/gputopo.h gt_tree): index 0 = root, gpu_id >= 0 marks a leaf."""
+    _fields_ = [("n_nodes", C.c_int32), ("parent", C.c_int32 * 32), ("gpu_id", C.c_int32 * 32),
+                ("access_cost", C.c_int32 * 32), ("level", C.c_int32 * 32)]
+
+
+def make_tree(spec):
+    """spec: nested tuples (level_code, child, ...) for topology nodes and (gpu_id, access_cost) pairs for leaves,
+    e.g. (LV_SYS, (LV_PXB, (0, 2), (1, 2)), (LV_PIX, (2, 1), (3, 1))); a node is a leaf when it has two ints."""
+    t = GtTree()
+    rows = []
+
+    def add(s, parent):
+        idx = len(rows)
+        if len(s) == 2 and all(isinstance(x, int) for x in s):
+            rows.append((parent, s[0], s[1], 0))
+        else:
+            rows.append((parent, -1, 0, int(s[0])))
+            for ch in s[1:]:
+                add(ch, idx)
+    add(spec, 0)
+    if len(rows) >= 32:
+        raise ValueError("a tree has at most 31 nodes")
+    t.n_nodes = len(rows)
+    for i, (p, g, a, l) in enumerate(rows):
+        t.parent[i], t.gpu_id[i], t.access_cost[i], t.level[i] = p, g, a, l
+    return t
+
+
+def tree_tables(tree):
+    """Host only: (levels[256], n_gpus, access_cost[16], sibling_mask[16]) a tree stands for."""
+    lv = np.zeros(256, np.uint8)
+    ng = C.c_uint8(0)
+    ac = np.zeros(16, np.uint8)
+    sib = np.zeros(16, np.uint16)
+    rc = _lib().gt_tree_tables(C.byref(tree), _p(lv, u8p), C.byref(ng), _p(ac, u8p), _p(sib, u16p))
+    if rc != 0:
+        raise GtError(rc, "gt_tree_tables")
+    return lv, ng.value, ac, sib
 
 
 class GtError(RuntimeError):
@@ -80,6 +122,9 @@ def _lib():
         getattr(L, f).argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     L.gt_load_nodes.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u8p, u8p, u16p, u16p]
     L.gt_update_free.argtypes = [C.c_void_p, u32p, u16p, C.c_uint32]
+    L.gt_tree_tables.argtypes = [C.POINTER(GtTree), u8p, C.POINTER(C.c_uint8), u8p, u16p]
+    L.gt_load_trees.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(GtTree), u16p]
+    L.gt_gaia_select.argtypes = [C.c_void_p, C.c_uint32, u32p]
     L.gt_score_all.argtypes = [C.c_void_p, C.c_void_p]
     L.gt_score_dirty.argtypes = [C.c_void_p]
     L.gt_best_node.argtypes = [C.c_void_p, u8p, C.c_uint32, u64p]
@@ -246,6 +291,19 @@ class Allocator:
         sib = np.ascontiguousarray(sibling_mask, np.uint16) if sibling_mask is not None else None
         self._ck(self._L.gt_load_nodes(self._h, first, count, _p(levels, u8p), _p(n_gpus, u8p), _p(ac, u8p),
                                        _p(sib, u16p), _p(free, u16p)), "gt_load_nodes")
+
+    def load_trees(self, trees, free, first=0):
+        """Nodes described by Gaia trees (list of GtTree): tables derived by the library, tree kept for gaia_select."""
+        arr = (GtTree * len(trees))(*trees)
+        free = np.ascontiguousarray(free, np.uint16)
+        assert free.shape[0] == len(trees)
+        self._ck(self._L.gt_load_trees(self._h, first, len(trees), arr, _p(free, u16p)), "gt_load_trees")
+
+    def gaia_select(self, m):
+        """Gaia Alg. 1 on the device for request size m: per node cost<<16|mask (m = 1 Singular, m >= 2 Link)."""
+        out = np.empty(self.num_nodes, np.uint32)
+        self._ck(self._L.gt_gaia_select(self._h, m, _p(out, u32p)), "gt_gaia_select")
+        return out
 
     def update_free(self, masks, node_ids=None):
         masks = np.ascontiguousarray(masks, np.uint16)

@@ -66,6 +66,8 @@ struct gt_ctx {
     uint8_t *d_levels = nullptr, *d_cost = nullptr, *d_ngpus = nullptr;
     uint8_t *d_access = nullptr;
     uint16_t *d_sibling = nullptr;
+    gt::TreeRow *d_tree = nullptr;              // Gaia trees (gt_load_trees); allocated on first use
+    uint32_t *d_gaia_out = nullptr;             // answers of gt_gaia_select
     uint16_t *d_free = nullptr;
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
@@ -543,6 +545,7 @@ void gt_destroy(gt_ctx *c)
     }
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_memo); cudaFree(c->d_row0); cudaFree(c->d_node_class); cudaFree(c->d_place);
+    cudaFree(c->d_tree); cudaFree(c->d_gaia_out);
     cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
@@ -616,6 +619,54 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
     if (rc != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));   // caller buffers are free to change after return
     c->best_valid = c->place_valid = false;
+    return GT_OK;
+}
+
+int gt_load_trees(gt_ctx *c, uint32_t first, uint32_t count, const gt_tree *trees, const uint16_t *free_mask)
+{
+    if (!c || !trees || !free_mask) return GT_ERR_INVALID;
+    if ((uint64_t)first + count > c->cap) return fail(c, GT_ERR_RANGE, "gt_load_trees: first+count exceeds max_nodes%s");
+    if (!count) return GT_OK;
+    std::vector<uint8_t> levels((size_t)count * 256), ng(count), access((size_t)count * 16);
+    std::vector<uint16_t> sibling((size_t)count * 16);
+    std::vector<gt::TreeRow> rows(count);
+    for (uint32_t i = 0; i < count; i++) {
+        if (i && memcmp(trees + i, trees + i - 1, sizeof(gt_tree)) == 0) {   // fleets repeat a few machine types
+            memcpy(&levels[(size_t)i * 256], &levels[(size_t)(i - 1) * 256], 256);
+            ng[i] = ng[i - 1];
+            memcpy(&access[(size_t)i * 16], &access[(size_t)(i - 1) * 16], 16);
+            memcpy(&sibling[(size_t)i * 16], &sibling[(size_t)(i - 1) * 16], 32);
+            rows[i] = rows[i - 1];
+            continue;
+        }
+        if (gt::tree_derive(trees + i, &levels[(size_t)i * 256], &ng[i], &access[(size_t)i * 16], &sibling[(size_t)i * 16],
+                            &rows[i]) != GT_OK)
+            return fail(c, GT_ERR_INVALID, "gt_load_trees: malformed tree%s");
+    }
+    GT_CUDA(c, cudaSetDevice(c->device));
+    if (!c->d_tree) {
+        GT_CUDA(c, cudaMalloc(&c->d_tree, (size_t)c->cap * sizeof(gt::TreeRow)));
+        GT_CUDA(c, cudaMemsetAsync(c->d_tree, 0, (size_t)c->cap * sizeof(gt::TreeRow), c->stream));
+    }
+    GT_CUDA(c, cudaMemcpyAsync(c->d_tree + first, rows.data(), (size_t)count * sizeof(gt::TreeRow), cudaMemcpyHostToDevice, c->stream));
+    return gt_load_nodes(c, first, count, levels.data(), ng.data(), access.data(), sibling.data(), free_mask);   // syncs the stream
+}
+
+int gt_gaia_select(gt_ctx *c, uint32_t m, uint32_t *out_best)
+{
+    if (!c || !out_best || m < 1 || m > 16) return GT_ERR_INVALID;
+    if (m >= 2 && !c->d_tree) return fail(c, GT_ERR_STATE, "gt_gaia_select: no tree loaded (gt_load_trees)%s");
+    if (!c->n_nodes) return GT_OK;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    int rc = flush_free(c, !c->free_uploaded);   // device masks = host mirror; the dirty list stays for the next scoring
+    if (rc != GT_OK) return rc;
+    if (!c->d_gaia_out) GT_CUDA(c, cudaMalloc(&c->d_gaia_out, (size_t)c->cap * 4));
+    gt::k_gaia_select<<<(c->n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+        c->d_tree, c->d_ngpus, c->d_free, c->d_access, c->d_sibling, c->d_cost, c->n_nodes, m, c->d_gaia_out);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    GT_CUDA(c, cudaMemcpyAsync(out_best, c->d_gaia_out, (size_t)c->n_nodes * 4, cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
     return GT_OK;
 }
 

@@ -20,6 +20,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "gaia_tree.h"
+
 namespace gt {
 
 constexpr int kMaxG = 16;
@@ -691,6 +693,86 @@ __global__ void __launch_bounds__(kCta) k_singular(const uint8_t *__restrict__ n
         if (key != ~0ull && (uint32_t)((key >> 16) & 0xFFFFFFFFu) == first_node + node)
             place[0] = (key & ~0xFFFFull) | v;
     }
+}
+
+// ---------------------------------------------------------------- Gaia Alg. 1 dispatch over tree inputs
+// m == 1: Alg. 3 Singular as in k_singular.  m >= 2: Alg. 4 Link (gpu_scheduler_algorithm_2.jpg): from every free
+// leaf (tree-index order) climb while fewer than m leaves are free beneath; the node where the climb stops is a
+// candidate with TotalCost = m x access cost of the m-th cheapest free leaf beneath it; lowest TotalCost, then the
+// candidate spanning fewer GPUs, then the first one met wins; its m cheapest free leaves (access cost, then id) are
+// handed out.  One thread per cluster node; the 128-byte tree row sits in the thread's local memory.
+// out[node] = pair-cost sum of the chosen set << 16 | mask, kInf when the node cannot serve m.
+__global__ void __launch_bounds__(kCta) k_gaia_select(const TreeRow *__restrict__ rows, const uint8_t *__restrict__ n_gpus,
+                                                      const uint16_t *__restrict__ free_mask,
+                                                      const uint8_t *__restrict__ access,
+                                                      const uint16_t *__restrict__ sibling,
+                                                      const uint8_t *__restrict__ cost, uint32_t n, uint32_t m,
+                                                      uint32_t *__restrict__ out)
+{
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n) return;
+    uint32_t ng = n_gpus[node];
+    ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
+    const uint32_t f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
+    union { uint4 q; uint8_t b[16]; } ac;
+    ac.q = __ldg(reinterpret_cast<const uint4 *>(access + (size_t)node * 16));
+    uint32_t result = kInf;
+    if (m == 1) {
+        if (f) {
+            int pick = -1, pick_any = -1;
+            uint32_t c1 = 0xFFFFFFFFu, c_any = 0xFFFFFFFFu;
+            for (uint32_t r = f; r; r &= r - 1) {
+                const int g = __ffs(r) - 1;
+                const uint32_t a = ac.b[g], sib = sibling[(size_t)node * 16 + g];
+                if (a < c_any) { c_any = a; pick_any = g; }
+                if (sib != 0 && (sib & f) == 0 && a < c1) { c1 = a; pick = g; }
+            }
+            result = 1u << (pick >= 0 ? pick : pick_any);
+        }
+    } else if ((uint32_t)__popc(f) >= m && rows != nullptr) {
+        union { uint4 q[8]; TreeRow r; } t;
+        const uint4 *src = reinterpret_cast<const uint4 *>(rows + node);
+#pragma unroll
+        for (int q = 0; q < 8; q++) t.q[q] = __ldg(src + q);
+        const uint32_t nt = t.r.n_tree;
+        int best = -1;
+        uint32_t best_cost = 0, best_size = 0;
+        for (uint32_t i = 0; i < nt; i++) {
+            if (!(t.r.parent[i] & 0x80u) || !(t.r.sub[i] & f)) continue;   // free leaves only
+            uint32_t a = i;
+            while ((uint32_t)__popc(t.r.sub[a] & f) < m && a != 0) a = t.r.parent[a] & 0x7Fu;
+            const uint32_t under = t.r.sub[a] & f;
+            if ((uint32_t)__popc(under) < m) continue;
+            uint32_t seen = 0, mth = 0;
+            for (int j = 0; j < 16; j++) {
+                const uint32_t g = t.r.order[j];
+                if (g == 0xFFu) break;
+                if ((under >> g) & 1u)
+                    if (++seen == m) { mth = g; break; }
+            }
+            const uint32_t tc = m * ac.b[mth], size = (uint32_t)__popc(t.r.sub[a]);
+            if (best < 0 || tc < best_cost || (tc == best_cost && size < best_size)) {
+                best = (int)a; best_cost = tc; best_size = size;
+            }
+        }
+        if (best >= 0) {
+            const uint32_t under = t.r.sub[best] & f;
+            uint32_t mask = 0, seen = 0;
+            for (int j = 0; j < 16 && seen < m; j++) {
+                const uint32_t g = t.r.order[j];
+                if (g == 0xFFu) break;
+                if ((under >> g) & 1u) { mask |= 1u << g; seen++; }
+            }
+            uint32_t sum = 0;
+            const uint8_t *tile = cost + (size_t)node * 256;
+            for (uint32_t r1 = mask; r1; r1 &= r1 - 1) {
+                const int g = __ffs(r1) - 1;
+                for (uint32_t r2 = r1 & (r1 - 1); r2; r2 &= r2 - 1) sum += tile[g * 16 + __ffs(r2) - 1];
+            }
+            result = (sum << 16) | mask;
+        }
+    }
+    out[node] = result;
 }
 
 // ---------------------------------------------------------------- "sort" verb: HostPriority scores 0..10

@@ -129,6 +129,36 @@ int gt_release(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32
 int gt_schedule(gt_ctx *ctx, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
                 uint16_t *out_mask, uint64_t *out_placed);
 
+/* ---- Gaia resource-access cost tree as an input format ---- */
+/* replaces: the tree T of the Gaia paper p. 255 (reference/gaia_gpu_topology/gpu_topology_tree.png, gaia.md:16-22):
+ * topology nodes labelled with a link level, GPU leaves with an id and an access cost.  Index 0 is the root;
+ * parent[0] is ignored.  gpu_id >= 0 marks a leaf; level[] is read for topology nodes (GT_LV_* code of the link
+ * its children share), access_cost[] for leaves (0..255). */
+#define GT_MAX_TREE_NODES 32
+typedef struct gt_tree {
+    int32_t n_nodes; /* 1 .. 31 (at most 2*16-1) */
+    int32_t parent[GT_MAX_TREE_NODES];
+    int32_t gpu_id[GT_MAX_TREE_NODES];
+    int32_t access_cost[GT_MAX_TREE_NODES];
+    int32_t level[GT_MAX_TREE_NODES];
+} gt_tree;
+/* host only: the tables a tree stands for -- pair level = label of the lowest common ancestor, sibling set =
+ * leaves under the same parent, access cost per GPU.  GT_ERR_INVALID for a malformed tree (cycle, duplicate or
+ * out-of-range GPU id, leaf used as a parent). */
+int gt_tree_tables(const gt_tree *tree, uint8_t out_levels[256], uint8_t *out_n_gpus, uint8_t out_access_cost[16],
+                   uint16_t out_sibling_mask[16]);
+/* gt_load_nodes for nodes described by trees: derives the tables above, loads them, and keeps the tree shape on
+ * the device for gt_gaia_select. */
+int gt_load_trees(gt_ctx *ctx, uint32_t first, uint32_t count, const gt_tree *trees, const uint16_t *free_mask);
+/* replaces: Gaia Alg. 1 dispatch (gpu_scheduler_algorithm.jpg; Fragment, 0 < m < 1, is skipped: gaia.md:36) on the
+ * device, one answer per node for request size m: m == 1 -> Alg. 3 Singular (gpu_scheduler_algorithm_1.png),
+ * m >= 2 -> Alg. 4 Link (gpu_scheduler_algorithm_2.jpg: from every free leaf climb until m leaves are free beneath,
+ * lowest m x access cost wins, then the smaller subtree; hand out its m cheapest free leaves).
+ * out_best[node] = pair-cost sum of the chosen set << 16 | mask (same word as gt_score_all's table), 0xFFFF0000
+ * when the node cannot serve m (for m >= 2 also a node that was loaded without a tree).  GT_ERR_STATE for m >= 2
+ * when no tree was ever loaded, GT_ERR_INVALID for m outside 1..16. */
+int gt_gaia_select(gt_ctx *ctx, uint32_t m, uint32_t *out_best);
+
 /* ---- the extender / device-plugin surface around the path (text formats are host only) ---- */
 /* replaces: topology discovery output design.md:27-29 -- the `nvidia-smi topo -m` table
  * (imgs/gpu_topology_on_machine.png) -> 16x16 level codes.  NV# with # > 4 maps to GT_LV_NVS. */
