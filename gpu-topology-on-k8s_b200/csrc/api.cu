@@ -238,11 +238,21 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
 // K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
 int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place)
 {
-    gt::k_bin<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-        c->d_ngpus, c->d_free, d_ids, n, c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best,
-        preset_place);
+    // programmatic dependent of the kernel in front of it (the previous pass's K1 in a scoring loop): the launch
+    // latency between two passes is spent while that kernel still runs; K0 waits inside for its completion
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((n + gt::kCta - 1) / gt::kCta);
+    cfg.blockDim = dim3(gt::kCta);
+    cfg.stream = c->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus, (const uint16_t *)c->d_free, d_ids, n,
+                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place));
     c->launches++;
-    GT_CUDA(c, cudaGetLastError());
     return GT_OK;
 }
 
@@ -1277,6 +1287,20 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
 }
 
 #ifdef GT_TRACE
+// debug builds only: kernel-level timeline of the last passes (ring of 64); resets the ring
+extern "C" int gt_debug_ktrace(gt_ctx *c, unsigned long long *out /* 64 x 8 */, uint32_t *out_pass)
+{
+    if (!c || !out || !out_pass) return GT_ERR_INVALID;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaMemcpyFromSymbol(out, gt::g_ktrace, sizeof(unsigned long long) * 64 * 8);
+    cudaMemcpyFromSymbol(out_pass, gt::g_kpass, 4);
+    unsigned long long init[64][8];
+    for (auto &r : init) { r[0] = ~0ull; r[1] = 0; r[2] = ~0ull; r[3] = ~0ull; r[4] = 0; r[5] = ~0ull; r[6] = r[7] = 0; }
+    cudaMemcpyToSymbol(gt::g_ktrace, init, sizeof init);
+    return GT_OK;
+}
+
 // debug builds only: the per-warp event trace of the last k_score launch
 extern "C" int gt_debug_trace(gt_ctx *c, unsigned long long *out, uint32_t n_words)
 {

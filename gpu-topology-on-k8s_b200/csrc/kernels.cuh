@@ -29,6 +29,9 @@ constexpr int kBins = 17;            // popcount 0..16
 constexpr int kCta = 256;
 constexpr uint32_t kInf = 0xFFFF0000u;
 constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
+#ifndef GT_K1_TRIGGER
+#define GT_K1_TRIGGER 2   // where K1 lets the next kernel's CTAs be scheduled: 0 = at exit, 1 = after its own wait, 2 = after its work loop
+#endif
 #ifndef GT_SCORE_MIN_CTAS
 #define GT_SCORE_MIN_CTAS 5
 #endif
@@ -61,6 +64,11 @@ __device__ __forceinline__ unsigned long long gt_now()
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
+// pass timeline: per pass (ring of 64) [K0 first entry, K0 last exit, K1 first entry, K1 after wait (first), K1 last exit]
+__device__ unsigned long long g_ktrace[64][8];
+__device__ unsigned int g_kpass;
+#define GT_KT_MIN(slot, t) atomicMin(&g_ktrace[g_kpass & 63u][slot], (t))
+#define GT_KT_MAX(slot, t) atomicMax(&g_ktrace[g_kpass & 63u][slot], (t))
 #define GT_TR(id)                                                                         \
     do {                                                                                  \
         if (lane == 0 && tr_n < kTraceSlots) tr[tr_n++] = (gt_now() << 8) | (unsigned)(id); \
@@ -131,7 +139,16 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
+#ifdef GT_TRACE
+    if (tid == 0) GT_KT_MIN(0, gt_now());
+#endif
     if (tid < kBins) s_cnt[tid] = 0;
+    // K0 is itself launched as a programmatic dependent of whatever kernel precedes it (normally the previous
+    // pass's K1): its CTAs become resident as that grid drains and wait here until it has completed and flushed.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+#ifdef GT_TRACE
+    if (tid == 0) GT_KT_MIN(5, gt_now());
+#endif
     if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
@@ -161,6 +178,9 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     // programmatic dependent launch: from here on K1's CTAs may be scheduled while this grid drains; K1 waits
     // (griddepcontrol.wait) for the whole grid before it reads the bins.  Triggering at the top of K0 instead
     // was measured 3-6 us slower per pass: the waiting K1 CTAs crowd K0 off the SMs.
+#ifdef GT_TRACE
+    if (tid == 0) GT_KT_MAX(1, gt_now());
+#endif
     asm volatile("griddepcontrol.launch_dependents;");
 }
 
@@ -435,9 +455,16 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     int tr_n = 0;
 #endif
     GT_TR(1);
+#ifdef GT_TRACE
+    const unsigned long long kt_entry = gt_now();
+#endif
     if (tid < 16) s_place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible (no-op without PDL)
     GT_TR(2);
+    if (GT_K1_TRIGGER == 1) asm volatile("griddepcontrol.launch_dependents;");
+#ifdef GT_TRACE
+    if (tid == 0) { GT_KT_MIN(2, kt_entry); GT_KT_MIN(3, gt_now()); }
+#endif
     // units per bin in hand-out order, then an inclusive scan inside warp 0 (17 lanes)
     if (warp == 0) {
         uint32_t units = 0, cnt = 0;
@@ -522,13 +549,21 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         atomicMin(&s_place[lane], key);
     }
     GT_TR(4);
+    if (GT_K1_TRIGGER == 2) asm volatile("griddepcontrol.launch_dependents;");
     __syncthreads();
     GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
     // the last CTA to finish leaves the control block zeroed for the next pass
     if (tid == 0) {
+#ifdef GT_TRACE
+        GT_KT_MAX(4, gt_now());
+        __threadfence();
+#endif
         const uint32_t done = atomicAdd(prm.ctl + kCtlDone, 1u);
         if (done == gridDim.x - 1) {
+#ifdef GT_TRACE
+            g_kpass++;
+#endif
             if (!prm.keep_bins)
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
