@@ -23,10 +23,12 @@ struct NcclApi {
     int (*GetUniqueId)(NcclId *) = nullptr;
     int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
     int (*CommDestroy)(void *) = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
 };
 constexpr int kNcclUint64 = 5;  // ncclUint64 in nccl.h
+constexpr int kNcclUint8 = 1;
 constexpr int kNcclMin = 3;     // ncclMin
 
 NcclApi *nccl_api()
@@ -44,6 +46,7 @@ NcclApi *nccl_api()
     api.GetUniqueId = (int (*)(NcclId *))dlsym(api.handle, "ncclGetUniqueId");
     api.CommInitRank = (int (*)(void **, int, NcclId, int))dlsym(api.handle, "ncclCommInitRank");
     api.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(api.handle, "ncclAllReduce");
+    api.AllGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(api.handle, "ncclAllGather");
     api.CommDestroy = (int (*)(void *))dlsym(api.handle, "ncclCommDestroy");
     api.GetErrorString = (const char *(*)(int))dlsym(api.handle, "ncclGetErrorString");
     if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy) {
@@ -72,7 +75,7 @@ struct gt_ctx {
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
     uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
-    unsigned long long *d_place = nullptr;      // [4][16]: [2],[3] = the two parities of the K0+K1 path, [0] NCCL warm-up
+    unsigned long long *d_place = nullptr;      // [4][16]: [2],[3] = the two parities of the K0+K1 path, [0] exchange warm-up
     unsigned long long *place_cur = nullptr;    // where the latest placement keys are
     cudaGraphExec_t step_exec[2] = {nullptr, nullptr};   // captured K0 + K1 of a full pass, per place parity
     uint32_t step_nodes = 0;                    // n_nodes the graphs were captured for
@@ -83,6 +86,12 @@ struct gt_ctx {
     cudaEvent_t ev_pass = nullptr, ev_comm[2] = {nullptr, nullptr};
     bool comm_used[2] = {false, false};
     int comm_last = -1;                         // parity whose exchange is the latest one in flight
+    // peer-memory exchange (k_exchange): every rank's inbox mapped through CUDA IPC; NCCL stays the fallback
+    bool p2p = false;
+    unsigned long long *d_inbox = nullptr;      // own inbox: keys[world][2][16] + flags[world][2]
+    unsigned long long *peer_inbox[gt::kMaxPeers] = {};
+    unsigned long long *d_xflags = nullptr;     // [0] K1's pass number, [1 + parity] number of the last finished exchange
+    uint64_t k1_seq = 0, xchg_seq = 0, parity_seq[2] = {0, 0};
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
@@ -229,6 +238,7 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
     p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
     p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
     p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
+    p.seq_flag = nullptr; p.seq = 0;
 #ifdef GT_TRACE
     p.trace = c->d_trace;
 #endif
@@ -236,7 +246,8 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
 }
 
 // K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
-int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place)
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place,
+               const unsigned long long *wait_flag = nullptr, unsigned long long wait_val = 0)
 {
     // programmatic dependent of the kernel in front of it (the previous pass's K1 in a scoring loop): the launch
     // latency between two passes is spent while that kernel still runs; K0 waits inside for its completion
@@ -251,12 +262,12 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus, (const uint16_t *)c->d_free, d_ids, n,
-                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place));
+                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place, wait_flag, wait_val));
     c->launches++;
     return GT_OK;
 }
 
-int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins = false)
+int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins = false, bool publish = false)
 {
     // persistent warps: every resident CTA slot, fewer when there is little work
     const uint32_t grid = std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::kScoreMinCtas);
@@ -271,7 +282,13 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     cfg.attrs = attr;
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
-    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, score_params(c, fold, keep_bins)));
+    gt::ScoreParams prm = score_params(c, fold, keep_bins);
+    if (publish) {
+        prm.seq_flag = c->d_xflags;
+        prm.seq = ++c->k1_seq;
+    }
+
+    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, prm));
     c->launches++;
     if (fold) c->place_cur = fold;
     return GT_OK;
@@ -288,26 +305,48 @@ int launch_singular(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long 
     return GT_OK;
 }
 
-// Multi-GPU: min of the 16 placement keys over all ranks, on the communication stream.  The pass that
-// produced `place` is ordered before it by an event; consumers wait for ev_comm[parity].
-int nccl_min(gt_ctx *c, unsigned long long *place, uint32_t parity)
+// Multi-GPU: min of the 16 placement keys over all ranks, on the communication stream; consumers wait for
+// ev_comm[parity].  With peer memory (c->p2p) this is k_exchange; `flag_ordered`: the producer was a K1 launched with
+// publish = true, the kernel waits for its flag itself and nothing is put between K1 and the next K0 on the scoring
+// stream (an event record there would cost the next K0 its programmatic launch).  Otherwise, and always on the NCCL
+// fallback, the pass that produced `place` is ordered before the exchange by an event.
+int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity, bool flag_ordered)
 {
     if (!c->comm) return GT_OK;
-    NcclApi *api = nccl_api();
-    GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
-    GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
-    int e = api->AllReduce(place, place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
-    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    if (!(c->p2p && flag_ordered)) {
+        GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
+        GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
+    }
+    if (c->p2p) {
+        gt::ExchangeParams prm = {};
+        prm.place = place;
+        prm.k1_flag = flag_ordered ? c->d_xflags : nullptr;
+        prm.k1_val = c->k1_seq;
+        for (int q = 0; q < c->world; q++) prm.inbox[q] = c->peer_inbox[q];
+        prm.done_flag = c->d_xflags + 1 + parity;
+        prm.seq = ++c->xchg_seq;
+        prm.rank = (uint32_t)c->rank; prm.world = (uint32_t)c->world; prm.parity = parity;
+        gt::k_exchange<<<1, 16 * gt::kMaxPeers, 0, c->comm_stream>>>(prm);
+        c->launches++;
+        GT_CUDA(c, cudaGetLastError());
+        c->parity_seq[parity] = prm.seq;
+    } else {
+        NcclApi *api = nccl_api();
+        int e = api->AllReduce(place, place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
+        if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    }
     GT_CUDA(c, cudaEventRecord(c->ev_comm[parity], c->comm_stream));
     c->comm_used[parity] = true;
     c->comm_last = (int)parity;
     return GT_OK;
 }
 
-// before a pass overwrites place[parity]: the exchange that last used that buffer must be finished
-int wait_place_free(gt_ctx *c, uint32_t parity)
+// before a pass overwrites place[parity]: the exchange that last used that buffer must be finished.
+// in_kernel: K0 itself waits for the exchange's done flag (launch_bin's wait_flag), nothing goes into the stream.
+int wait_place_free(gt_ctx *c, uint32_t parity, bool in_kernel)
 {
-    if (c->comm && c->comm_used[parity]) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[parity], 0));
+    if (c->comm && c->comm_used[parity] && !(c->p2p && in_kernel))
+        GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[parity], 0));
     return GT_OK;
 }
 
@@ -405,23 +444,32 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
     int rc;
     const uint32_t par = c->bin_parity;
-    if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
+    const bool memo_pass = !d_ids && n && (c->flags & GT_FLAG_MEMO_PASS) && !c->memo_pass_failed;
+    const bool graph = !d_ids && n && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed;
+    // plain K0 -> K1 pass with peers: all cross-stream ordering through device flags (see exchange_min)
+    bool flagged = c->comm && c->p2p && !d_ids && n && !memo_pass && !graph && c->k1_policy != GT_K1_GAIA_SINGULAR;
+    if ((rc = wait_place_free(c, par, flagged)) != GT_OK) return rc;
     if (!d_ids && n) {
         bool done = false;
-        if ((c->flags & GT_FLAG_MEMO_PASS) && !c->memo_pass_failed) {
+        if (memo_pass) {
             rc = launch_memo_pass(c, bin_place(c, par));
             if (rc == GT_ERR_RANGE) c->memo_pass_failed = true;   // too many topology classes: enumerate as usual
             else if (rc != GT_OK) return rc;
             else done = true;
         }
-        if (!done && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed) {   // measured slower than two plain launches: opt-in
+        if (!done && graph) {   // measured slower than two plain launches: opt-in
             done = launch_step_graph(c, par) == GT_OK;
             if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
         }
         if (!done) {
-            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
-            if ((rc = launch_score(c, n, bin_place(c, par))) != GT_OK) return rc;
+            // flagged: K0's block 0 itself waits for the exchange that last used this key buffer before presetting it
+            const bool wait_in_k0 = flagged && c->comm_used[par];
+            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par), wait_in_k0 ? c->d_xflags + 1 + par : nullptr,
+                                 c->parity_seq[par])) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, bin_place(c, par), false, flagged)) != GT_OK) return rc;
             if ((rc = launch_singular(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
+        } else {
+            flagged = false;
         }
     } else {
         if (n) {
@@ -431,7 +479,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
         }
         if ((rc = launch_argmin(c)) != GT_OK) return rc;
     }
-    if ((rc = nccl_min(c, c->place_cur, par)) != GT_OK) return rc;
+    if ((rc = exchange_min(c, c->place_cur, par, flagged)) != GT_OK) return rc;
     c->bin_parity ^= 1u;
     c->best_valid = true;
     c->place_valid = true;
@@ -508,6 +556,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
+        GT_CUDA(c, cudaMalloc(&c->d_xflags, 4 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMemset(c->d_xflags, 0, 4 * sizeof(unsigned long long)));
         GT_CUDA(c, cudaHostAlloc(&c->h_scores, (N + 3) / 4 * 4, cudaHostAllocMapped));
         GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_scores_map, c->h_scores, 0));
         GT_CUDA(c, cudaHostAlloc(&c->h_place_map, 16 * sizeof(unsigned long long), cudaHostAllocMapped));
@@ -556,6 +606,9 @@ void gt_destroy(gt_ctx *c)
     cudaFree(c->d_levels); cudaFree(c->d_cost); cudaFree(c->d_ngpus); cudaFree(c->d_access); cudaFree(c->d_sibling);
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_memo); cudaFree(c->d_row0); cudaFree(c->d_node_class); cudaFree(c->d_place);
     cudaFree(c->d_tree); cudaFree(c->d_gaia_out);
+    for (int q = 0; q < gt::kMaxPeers; q++)
+        if (c->peer_inbox[q] && c->peer_inbox[q] != c->d_inbox) cudaIpcCloseMemHandle(c->peer_inbox[q]);
+    cudaFree(c->d_inbox); cudaFree(c->d_xflags);
     cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
@@ -844,6 +897,7 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
         explicit CommOff(gt_ctx *x) : c(x), saved(x->comm) { x->comm = nullptr; }
         ~CommOff() { c->comm = saved; c->place_valid = false; }
     } comm_off(c);
+    if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));   // no exchange may still be reading the key buffers
     int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
     if (rc != GT_OK) return rc;
     clear_dirty(c);
@@ -896,6 +950,76 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     return GT_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+// Peer-memory exchange: every rank allocates an inbox, the CUDA IPC handles travel once through ncclAllGather and
+// each rank maps the others' inboxes.  All ranks agree (min all-reduce of a success word) whether to use it;
+// otherwise -- ranks without peer access, more than kMaxPeers ranks, GT_NO_P2P set -- the exchange stays the NCCL
+// all-reduce.  Ranks must be separate processes (an IPC handle cannot be opened by the process that made it).
+int setup_peer_exchange(gt_ctx *c)
+{
+    NcclApi *api = nccl_api();
+    const int world = c->world;
+    if (world < 2) return GT_OK;
+    unsigned long long ok = (world <= gt::kMaxPeers && api->AllGather && getenv("GT_NO_P2P") == nullptr) ? 1 : 0;
+    const size_t inbox_words = (size_t)world * 32 + (size_t)world * 2;
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof mine);
+    unsigned char *d_handles = nullptr;
+    unsigned long long *d_ok = nullptr;
+    std::vector<cudaIpcMemHandle_t> all((size_t)world);
+    GT_CUDA(c, cudaMalloc(&d_handles, (size_t)(world + 1) * sizeof(cudaIpcMemHandle_t)));
+    GT_CUDA(c, cudaMalloc(&d_ok, sizeof(unsigned long long)));
+    if (ok) {
+        if (cudaMalloc(&c->d_inbox, inbox_words * 8) != cudaSuccess || cudaMemset(c->d_inbox, 0, inbox_words * 8) != cudaSuccess ||
+            cudaIpcGetMemHandle(&mine, c->d_inbox) != cudaSuccess) {
+            cudaGetLastError();
+            ok = 0;
+        }
+    }
+    // handles to everybody (a zero handle from a rank that could not make one)
+    GT_CUDA(c, cudaMemcpy(d_handles + (size_t)world * sizeof mine, &mine, sizeof mine, cudaMemcpyHostToDevice));
+    int e = api->AllGather ? api->AllGather(d_handles + (size_t)world * sizeof mine, d_handles, sizeof mine, kNcclUint8, c->comm, c->comm_stream) : 0;
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllGather: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    GT_CUDA(c, cudaMemcpy(all.data(), d_handles, (size_t)world * sizeof mine, cudaMemcpyDeviceToHost));
+    if (ok) {
+        for (int q = 0; q < world && ok; q++) {
+            if (q == c->rank) { c->peer_inbox[q] = c->d_inbox; continue; }
+            void *ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                ok = 0;
+            } else {
+                c->peer_inbox[q] = (unsigned long long *)ptr;
+            }
+        }
+    }
+    // unanimous or not at all
+    GT_CUDA(c, cudaMemcpy(d_ok, &ok, sizeof ok, cudaMemcpyHostToDevice));
+    e = api->AllReduce(d_ok, d_ok, 1, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    GT_CUDA(c, cudaMemcpy(&ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost));
+    cudaFree(d_handles);
+    cudaFree(d_ok);
+    c->p2p = ok != 0;
+    if (!c->p2p) return GT_OK;
+    // one exchange now: first touch of the peer mappings happens before any timed pass
+    int rc = exchange_min(c, c->d_place, 0, false);
+    if (rc != GT_OK) return rc;
+    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    c->comm_used[0] = false;
+    c->comm_last = -1;
+    return GT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
 int gt_comm_unique_id(uint8_t out_id[128])
 {
     NcclApi *api = nccl_api();
@@ -930,7 +1054,7 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce (warm-up): %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     c->place_valid = false;
-    return GT_OK;
+    return setup_peer_exchange(c);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1272,10 +1396,11 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr);
+                                                                     nullptr, nullptr, 0ull);
     gt::ScoreParams prm;
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;
+    prm.seq_flag = nullptr; prm.seq = 0;
 #ifdef GT_TRACE
     return static_fail(GT_ERR_STATE, err_buf, err_len, "trace build: gt_score_nodes_static is disabled");
 #endif

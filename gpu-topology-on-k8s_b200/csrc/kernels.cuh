@@ -52,6 +52,8 @@ struct ScoreParams {
     uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
+    unsigned long long *seq_flag;   // multi-GPU: the last CTA publishes `seq` here once every fold into `place` is done
+    unsigned long long seq;         // (k_exchange on the communication stream waits for it; null = nobody waits)
 #ifdef GT_TRACE
     unsigned long long *trace;   // [warps][kTraceSlots] (globaltimer ns << 8 | event id), debug builds only
 #endif
@@ -135,7 +137,8 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               const uint32_t *__restrict__ ids, uint32_t n, uint32_t cap,
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
-                                              unsigned long long *__restrict__ place)
+                                              unsigned long long *__restrict__ place,
+                                              const unsigned long long *wait_flag, unsigned long long wait_val)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
@@ -149,7 +152,12 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 #ifdef GT_TRACE
     if (tid == 0) GT_KT_MIN(5, gt_now());
 #endif
-    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
+    if (place && blockIdx.x == 0 && tid < 16) {
+        // multi-GPU: the exchange that last used this key buffer (two passes ago) must have finished with it
+        if (wait_flag)
+            while (*reinterpret_cast<const volatile unsigned long long *>(wait_flag) < wait_val) __nanosleep(64);
+        place[tid] = ~0ull;
+    }
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
     int p = -1;
@@ -553,6 +561,10 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     __syncthreads();
     GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
+    if (prm.seq_flag) {       // somebody reads `place` without a kernel boundary: order the folds before the count
+        __syncthreads();
+        if (tid == 0) __threadfence();
+    }
     // the last CTA to finish leaves the control block zeroed for the next pass
     if (tid == 0) {
 #ifdef GT_TRACE
@@ -568,8 +580,67 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
             prm.ctl[kCtlDone] = 0u;
+            if (prm.seq_flag) {
+                __threadfence();
+                *reinterpret_cast<volatile unsigned long long *>(prm.seq_flag) = prm.seq;
+            }
         }
     }
+}
+
+// ---------------------------------------------------------------- multi-GPU: min-exchange of the 16 placement keys
+// One CTA per GPU on the communication stream, all GPUs of one NVLink domain (peer memory mapped through CUDA IPC).
+// Every rank stores its 16 keys into every rank's inbox, fences, raises its flag there with the exchange number, waits
+// until all flags of its own inbox carry that number and reduces the world x 16 keys with min -- one store and one
+// flag round trip over NVLink, no host involvement and nothing in front of the next pass on the scoring stream:
+// the kernel can be enqueued before K1 has run and waits for K1's `seq_flag` itself.
+// Inbox (u64 words): keys[world][2 parities][16], then flags[world][2].  Parities alternate between passes, and a
+// rank reuses a parity only after its previous exchange on the other parity completed, i.e. after every peer has
+// entered that one -- by stream order the peers have then finished reading this parity.
+constexpr int kMaxPeers = 8;
+struct ExchangeParams {
+    unsigned long long *place;            // 16 local keys in, 16 reduced keys out
+    const unsigned long long *k1_flag;    // null: the stream already orders this kernel after the producer
+    unsigned long long k1_val;
+    unsigned long long *inbox[kMaxPeers]; // inbox base of every rank (own address for the own rank)
+    unsigned long long *done_flag;        // local: exchange number written when `place` holds the result
+    unsigned long long seq;               // exchange number, the same on every rank
+    uint32_t rank, world, parity;
+};
+// 16 x kMaxPeers threads on purpose: measured against a one-warp version, which leaves room beside K1's five CTAs
+// per SM, sits there spinning through the whole pass and costs the scoring stream 1.3 us per pass (K1's programmatic
+// launch is slower while another grid is resident); this size only gets onto an SM once K1 drains.
+__global__ void __launch_bounds__(16 * kMaxPeers) k_exchange(ExchangeParams prm)
+{
+    const uint32_t tid = threadIdx.x, k = tid & 15u, q = tid >> 4;
+    if (tid == 0 && prm.k1_flag)
+        while (*reinterpret_cast<const volatile unsigned long long *>(prm.k1_flag) < prm.k1_val) __nanosleep(100);
+    __syncthreads();
+    const uint32_t slot = prm.rank * 2 + prm.parity;
+    if (q < prm.world) {
+        const unsigned long long key = *reinterpret_cast<volatile unsigned long long *>(prm.place + k);
+        *reinterpret_cast<volatile unsigned long long *>(prm.inbox[q] + (size_t)slot * 16 + k) = key;
+    }
+    __threadfence_system();
+    __syncthreads();
+    const size_t flags = (size_t)prm.world * 32;
+    if (tid < prm.world) *reinterpret_cast<volatile unsigned long long *>(prm.inbox[tid] + flags + slot) = prm.seq;
+    unsigned long long *mine = prm.inbox[prm.rank];
+    if (tid < prm.world)
+        while (*reinterpret_cast<volatile unsigned long long *>(mine + flags + tid * 2 + prm.parity) < prm.seq) __nanosleep(32);
+    __threadfence_system();
+    __syncthreads();
+    if (tid < 16) {
+        unsigned long long m = ~0ull;
+        for (uint32_t r = 0; r < prm.world; r++) {
+            const unsigned long long v = *reinterpret_cast<volatile unsigned long long *>(mine + (size_t)(r * 2 + prm.parity) * 16 + tid);
+            m = v < m ? v : m;
+        }
+        prm.place[tid] = m;
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) *reinterpret_cast<volatile unsigned long long *>(prm.done_flag) = prm.seq;
 }
 
 // ---------------------------------------------------------------- K2: best node per k
