@@ -28,7 +28,7 @@ EXPORTS = [
     "gt_comm_unique_id", "gt_comm_init", "gt_synth_cluster", "gt_score_nodes_static", "gt_schedule", "gt_synth_events",
     "gt_parse_topo_matrix", "gt_annotation_encode", "gt_annotation_decode", "gt_group_encode", "gt_group_decode",
     "gt_bind_annotations", "gt_ext_sort", "gt_ext_bind", "gt_plugin_allocate",
-    "gt_tree_tables", "gt_load_trees", "gt_gaia_select",
+    "gt_tree_tables", "gt_load_trees", "gt_gaia_select", "gt_comm_mode",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -125,6 +125,7 @@ def _lib():
     L.gt_tree_tables.argtypes = [C.POINTER(GtTree), u8p, C.POINTER(C.c_uint8), u8p, u16p]
     L.gt_load_trees.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(GtTree), u16p]
     L.gt_gaia_select.argtypes = [C.c_void_p, C.c_uint32, u32p]
+    L.gt_comm_mode.argtypes = [C.c_void_p]
     L.gt_score_all.argtypes = [C.c_void_p, C.c_void_p]
     L.gt_score_dirty.argtypes = [C.c_void_p]
     L.gt_best_node.argtypes = [C.c_void_p, u8p, C.c_uint32, u64p]
@@ -304,6 +305,10 @@ class Allocator:
         out = np.empty(self.num_nodes, np.uint32)
         self._ck(self._L.gt_gaia_select(self._h, m, _p(out, u32p)), "gt_gaia_select")
         return out
+
+    def comm_mode(self):
+        """0 = no communicator, 1 = NCCL all-reduce, 2 = own kernel over peer memory"""
+        return int(self._L.gt_comm_mode(self._h))
 
     def update_free(self, masks, node_ids=None):
         masks = np.ascontiguousarray(masks, np.uint16)

@@ -82,7 +82,8 @@ struct gt_ctx {
     bool graph_failed = false;
     uint32_t bin_parity = 0;                    // placement-key buffer the next pass writes
     // multi-GPU: the 128-byte min-exchange runs on its own stream so it overlaps the next pass
-    cudaStream_t comm_stream = nullptr;
+    cudaStream_t comm_stream = nullptr;         // shared by the contexts of this process on the same device (see comm_stream_for)
+    bool own_comm_stream = false;
     cudaEvent_t ev_pass = nullptr, ev_comm[2] = {nullptr, nullptr};
     bool comm_used[2] = {false, false};
     int comm_last = -1;                         // parity whose exchange is the latest one in flight
@@ -614,7 +615,10 @@ void gt_destroy(gt_ctx *c)
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     for (auto &g : c->step_exec)
         if (g) cudaGraphExecDestroy(g);
-    if (c->comm_stream) { cudaStreamSynchronize(c->comm_stream); cudaStreamDestroy(c->comm_stream); }
+    if (c->comm_stream) {
+        cudaStreamSynchronize(c->comm_stream);
+        if (c->own_comm_stream) cudaStreamDestroy(c->comm_stream);
+    }
     if (c->ev_h2d) cudaEventDestroy(c->ev_h2d);
     if (c->ev_pass) cudaEventDestroy(c->ev_pass);
     for (auto &e : c->ev_comm)
@@ -954,6 +958,28 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
 
 namespace {
 
+// One communication stream per device and process: the exchanges of several contexts on a device (bench.py rotates
+// eight cluster replicas) run one after the other in the order their passes were issued.  With a stream each, the
+// exchange kernels of all of them sat on the SMs at once, each waiting for its own K1, and every pass paid for it
+// (K1's programmatic launch is slower while other grids are resident).  The price is an ordering rule NCCL users know:
+// every rank issues the passes of its contexts on a device in the same order.  GT_PRIVATE_COMM_STREAM: one per context.
+int comm_stream_for(gt_ctx *c)
+{
+    static std::mutex mu;
+    static cudaStream_t shared[64] = {};
+    static const bool priv = getenv("GT_PRIVATE_COMM_STREAM") != nullptr;
+    if (priv || c->device < 0 || c->device >= 64) {
+        GT_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+        c->own_comm_stream = true;
+        return GT_OK;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!shared[c->device]) GT_CUDA(c, cudaStreamCreateWithFlags(&shared[c->device], cudaStreamNonBlocking));
+    c->comm_stream = shared[c->device];
+    c->own_comm_stream = false;
+    return GT_OK;
+}
+
 // Peer-memory exchange: every rank allocates an inbox, the CUDA IPC handles travel once through ncclAllGather and
 // each rank maps the others' inboxes.  All ranks agree (min all-reduce of a success word) whether to use it;
 // otherwise -- ranks without peer access, more than kMaxPeers ranks, GT_NO_P2P set -- the exchange stays the NCCL
@@ -1020,6 +1046,8 @@ int setup_peer_exchange(gt_ctx *c)
 
 extern "C" {
 
+int gt_comm_mode(const gt_ctx *c) { return !c || !c->comm ? 0 : (c->p2p ? 2 : 1); }
+
 int gt_comm_unique_id(uint8_t out_id[128])
 {
     NcclApi *api = nccl_api();
@@ -1045,7 +1073,8 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     }
     c->rank = rank;
     c->world = world;
-    GT_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    int rcs = comm_stream_for(c);
+    if (rcs != GT_OK) return rcs;
     GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_pass, cudaEventDisableTiming));
     for (auto &ev : c->ev_comm) GT_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     // one exchange now, so connections are set up before any timed or latency-critical pass

@@ -227,6 +227,9 @@ int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_gpus, const 
 /* ---- multi-GPU: nodes are sharded, one context per GPU; the only exchange is a min over 16 keys ---- */
 int gt_comm_unique_id(uint8_t out_id[128]);
 int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
+/* how the placement keys travel between ranks: 0 = no communicator, 1 = NCCL all-reduce, 2 = own kernel over peer
+ * memory (ranks are separate processes on one NVLink domain that could map each other's inbox through CUDA IPC) */
+int gt_comm_mode(const gt_ctx *ctx);
 
 /* ---- synthetic clusters for tests and benchmarks (splitmix64) ---- */
 int gt_synth_cluster(int config, uint64_t seed, uint32_t first, uint32_t count, uint8_t *levels,
