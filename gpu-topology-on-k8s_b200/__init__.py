@@ -29,6 +29,8 @@ EXPORTS = [
     "gt_parse_topo_matrix", "gt_annotation_encode", "gt_annotation_decode", "gt_group_encode", "gt_group_decode",
     "gt_bind_annotations", "gt_ext_sort", "gt_ext_bind", "gt_plugin_allocate",
     "gt_tree_tables", "gt_load_trees", "gt_gaia_select", "gt_comm_mode",
+    "gt_wire_parse_extender_args", "gt_wire_host_priorities", "gt_wire_parse_binding_args", "gt_wire_binding_result",
+    "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -126,6 +128,15 @@ def _lib():
     L.gt_load_trees.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(GtTree), u16p]
     L.gt_gaia_select.argtypes = [C.c_void_p, C.c_uint32, u32p]
     L.gt_comm_mode.argtypes = [C.c_void_p]
+    L.gt_wire_parse_extender_args.argtypes = [C.c_char_p, C.c_size_t, u32p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
+                                              C.POINTER(C.c_int32)]
+    L.gt_wire_host_priorities.argtypes = [C.c_char_p, C.c_uint32, u8p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.gt_wire_parse_binding_args.argtypes = [C.c_char_p, C.c_size_t] + [C.c_char_p, C.c_size_t] * 4
+    L.gt_wire_binding_result.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
+    L.gt_set_node_names.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
+    L.gt_ext_sort_json.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.gt_ext_bind_json.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_int64, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    L.gt_ext_pod_deleted.argtypes = [C.c_void_p, C.c_char_p]
     L.gt_score_all.argtypes = [C.c_void_p, C.c_void_p]
     L.gt_score_dirty.argtypes = [C.c_void_p]
     L.gt_best_node.argtypes = [C.c_void_p, u8p, C.c_uint32, u64p]
@@ -462,6 +473,88 @@ EXTENDER_POLICY = {
     }],
 }
 RESOURCE_NAME = "aliyun.com/gpu"
+
+
+def wire_parse_extender_args(body):
+    """ExtenderArgs JSON (bytes or str) -> (gpu_count, pod uid, node names or None when the field is absent)."""
+    if isinstance(body, str):
+        body = body.encode()
+    cnt, n = C.c_uint32(0), C.c_int32(0)
+    uid = C.create_string_buffer(256)
+    names = C.create_string_buffer(len(body) + 1)
+    rc = _lib().gt_wire_parse_extender_args(body, len(body), C.byref(cnt), uid, len(uid), names, len(names), C.byref(n))
+    if rc:
+        raise GtError(rc, "gt_wire_parse_extender_args")
+    lst = None if n.value < 0 else (names.value.decode().split("\n") if n.value else [])
+    return cnt.value, uid.value.decode(), lst
+
+
+def wire_host_priorities(names, scores):
+    """HostPriorityList JSON text for node names and their scores."""
+    scores = np.ascontiguousarray(scores, np.uint8)
+    joined = "\n".join(names).encode()
+    out = C.create_string_buffer(len(joined) * 6 + 32 * len(names) + 16)
+    n = C.c_size_t(0)
+    rc = _lib().gt_wire_host_priorities(joined, len(names), _p(scores, u8p), out, len(out), C.byref(n))
+    if rc:
+        raise GtError(rc, "gt_wire_host_priorities")
+    return out.value.decode()
+
+
+def wire_parse_binding_args(body):
+    """ExtenderBindingArgs JSON -> dict(PodName, PodNamespace, PodUID, Node)."""
+    if isinstance(body, str):
+        body = body.encode()
+    bufs = [C.create_string_buffer(len(body) + 1) for _ in range(4)]
+    args = []
+    for b in bufs:
+        args += [b, len(b)]
+    rc = _lib().gt_wire_parse_binding_args(body, len(body), *args)
+    if rc:
+        raise GtError(rc, "gt_wire_parse_binding_args")
+    return dict(zip(("PodName", "PodNamespace", "PodUID", "Node"), (b.value.decode() for b in bufs)))
+
+
+def wire_binding_result(error=""):
+    out = C.create_string_buffer(len(error.encode()) * 6 + 32)
+    rc = _lib().gt_wire_binding_result(error.encode(), out, len(out))
+    if rc:
+        raise GtError(rc, "gt_wire_binding_result")
+    return out.value.decode()
+
+
+class ExtenderHTTP:
+    """What the reference's HTTP handlers do with a request body (design.md:92-121), on the C-ABI's JSON entry points:
+    `handle("sort", body)` / `handle("bind", body)` return the reply body; no server is started here."""
+
+    def __init__(self, allocator, node_names):
+        self.alloc = allocator
+        joined = "\n".join(node_names).encode()
+        allocator._ck(allocator._L.gt_set_node_names(allocator._h, joined, len(joined)), "gt_set_node_names")
+        self.annotations = {}      # pod uid -> annotations written by the last bind
+
+    def handle(self, verb, body, now=0):
+        if isinstance(body, str):
+            body = body.encode()
+        a = self.alloc
+        if verb == "sort":
+            out = C.create_string_buffer(64 * a.num_nodes + len(body) * 6 + 64)
+            n = C.c_size_t(0)
+            a._ck(a._L.gt_ext_sort_json(a._h, body, len(body), out, len(out), C.byref(n)), "gt_ext_sort_json")
+            return out.raw[:n.value].decode()
+        if verb == "bind":
+            out = C.create_string_buffer(1024)
+            ann = C.create_string_buffer(256)
+            a._ck(a._L.gt_ext_bind_json(a._h, body, len(body), now, out, len(out), ann, len(ann)), "gt_ext_bind_json")
+            if ann.value:
+                uid = wire_parse_binding_args(body)["PodUID"]
+                self.annotations[uid] = dict(l.split(": ", 1) for l in ann.value.decode().splitlines())
+            return out.value.decode()
+        raise ValueError("the extender has no %r verb (design.md:117: sort and bind only)" % verb)
+
+    def pod_deleted(self, uid):
+        a = self.alloc
+        a._ck(a._L.gt_ext_pod_deleted(a._h, uid.encode()), "gt_ext_pod_deleted")
 
 
 class Extender:

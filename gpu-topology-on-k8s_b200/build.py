@@ -4,8 +4,8 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(HERE, "libgputopo.so")
-SOURCES = [os.path.join(HERE, "csrc", f) for f in ("api.cu", "host.cc", "extender.cc", "gaia_tree.cc")]
-DEPS = SOURCES + [os.path.join(HERE, "csrc", "kernels.cuh"), os.path.join(HERE, "csrc", "gaia_tree.h"),
+SOURCES = [os.path.join(HERE, "csrc", f) for f in ("api.cu", "host.cc", "extender.cc", "gaia_tree.cc", "wire.cc")]
+DEPS = SOURCES + [os.path.join(HERE, "csrc", "kernels.cuh"), os.path.join(HERE, "csrc", "gaia_tree.h"), os.path.join(HERE, "csrc", "wire.h"),
                   os.path.join(os.path.dirname(HERE), "include", "gputopo.h")]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -2,6 +2,7 @@
 // No CPU fallback lives here: scoring only ever happens in the kernels of kernels.cuh.
 #include "../../include/gputopo.h"
 #include "kernels.cuh"
+#include "wire.h"
 
 #include <dlfcn.h>
 
@@ -89,6 +90,11 @@ struct gt_ctx {
     int comm_last = -1;                         // parity whose exchange is the latest one in flight
     // peer-memory exchange (k_exchange): every rank's inbox mapped through CUDA IPC; NCCL stays the fallback
     bool p2p = false;
+    // extender handlers on JSON bodies: node names, pods between sort and bind, pods bound
+    std::vector<std::string> node_names;
+    std::unordered_map<std::string, uint32_t> node_index;
+    std::unordered_map<std::string, uint32_t> pod_request;                       // uid -> GPUs asked for (from sort)
+    std::unordered_map<std::string, std::pair<uint32_t, uint16_t>> pod_bound;    // uid -> (node, GPUs)
     unsigned long long *d_inbox = nullptr;      // own inbox: keys[world][2][16] + flags[world][2]
     unsigned long long *peer_inbox[gt::kMaxPeers] = {};
     unsigned long long *d_xflags = nullptr;     // [0] K1's pass number, [1 + parity] number of the last finished exchange
@@ -1318,6 +1324,98 @@ int gt_ext_bind(gt_ctx *c, uint32_t node, uint32_t m, int64_t assume_time, uint1
     *out_mask = mask;
     if (out_annotations && cap) rc = gt_bind_annotations(mask, assume_time, 0, out_annotations, cap);
     return rc;
+}
+
+int gt_set_node_names(gt_ctx *c, const char *names, size_t len)
+{
+    if (!c || (!names && len)) return GT_ERR_INVALID;
+    std::vector<std::string> v;
+    size_t s0 = 0;
+    for (size_t i = 0; i <= len; i++)
+        if (i == len || names[i] == '\n') {
+            if (i > s0 || i < len) v.emplace_back(names + s0, i - s0);
+            s0 = i + 1;
+        }
+    if (v.size() > c->cap) return fail(c, GT_ERR_RANGE, "gt_set_node_names: more names than max_nodes%s");
+    c->node_index.clear();
+    for (uint32_t i = 0; i < v.size(); i++)
+        if (v[i].empty() || !c->node_index.emplace(v[i], i).second)
+            return fail(c, GT_ERR_INVALID, "gt_set_node_names: empty or duplicate name '%s'", v[i].c_str());
+    c->node_names.swap(v);
+    return GT_OK;
+}
+
+int gt_ext_sort_json(gt_ctx *c, const char *request, size_t len, char *out, size_t cap, size_t *out_len)
+{
+    if (!c || !request || !out) return GT_ERR_INVALID;
+    if (c->node_names.size() != c->n_nodes) return fail(c, GT_ERR_STATE, "gt_ext_sort_json: gt_set_node_names first%s");
+    gt::ExtenderArgsWire a;
+    int rc = gt::parse_extender_args(request, len, &a);
+    if (rc != GT_OK) return fail(c, rc, "gt_ext_sort_json: malformed ExtenderArgs%s");
+    if (a.gpu_count < 1 || a.gpu_count > 16)
+        return fail(c, GT_ERR_INVALID, "gt_ext_sort_json: the pod asks for no or more than 16 " GT_RESOURCE_NAME "%s");
+    std::vector<uint8_t> scores(c->n_nodes ? c->n_nodes : 1);
+    if ((rc = gt_ext_sort(c, a.gpu_count, scores.data(), nullptr)) != GT_OK) return rc;
+    if (!a.uid.empty()) c->pod_request[a.uid] = a.gpu_count;
+    std::string s = "[";
+    auto item = [&](const std::string &name, unsigned score, bool first) {
+        if (!first) s.push_back(',');
+        s += "{\"Host\":";
+        gt::json_escape(name, &s);
+        s += ",\"Score\":" + std::to_string(score) + "}";
+    };
+    if (a.has_names) {
+        for (size_t i = 0; i < a.names.size(); i++) {
+            auto it = c->node_index.find(a.names[i]);
+            item(a.names[i], it == c->node_index.end() ? 0u : scores[it->second], i == 0);
+        }
+    } else {
+        for (uint32_t i = 0; i < c->n_nodes; i++) item(c->node_names[i], scores[i], i == 0);
+    }
+    s.push_back(']');
+    if (out_len) *out_len = s.size();
+    if (s.size() + 1 > cap) return fail(c, GT_ERR_RANGE, "gt_ext_sort_json: reply buffer too small%s");
+    memcpy(out, s.c_str(), s.size() + 1);
+    return GT_OK;
+}
+
+int gt_ext_bind_json(gt_ctx *c, const char *request, size_t len, int64_t assume_time, char *out, size_t cap,
+                     char *out_annotations, size_t ann_cap)
+{
+    if (!c || !request || !out) return GT_ERR_INVALID;
+    if (out_annotations && ann_cap) out_annotations[0] = 0;
+    gt::BindingArgsWire b;
+    int rc = gt::parse_binding_args(request, len, &b);
+    if (rc != GT_OK) return fail(c, rc, "gt_ext_bind_json: malformed ExtenderBindingArgs%s");
+    std::string err;
+    auto pod = c->pod_request.find(b.pod_uid);
+    auto node = c->node_index.find(b.node);
+    if (pod == c->pod_request.end()) err = "pod " + b.pod_uid + " was not seen by sort";
+    else if (node == c->node_index.end() || node->second >= c->n_nodes) err = "unknown node " + b.node;
+    else if (c->pod_bound.count(b.pod_uid)) err = "pod " + b.pod_uid + " is already bound";
+    else {
+        uint16_t mask = 0;
+        rc = gt_ext_bind(c, node->second, pod->second, assume_time, &mask, out_annotations, ann_cap);
+        if (rc == GT_OK) {
+            c->pod_bound[b.pod_uid] = std::make_pair(node->second, mask);
+            c->pod_request.erase(pod);
+        } else {
+            err = std::string(gt_strerror(rc)) + ": " + c->err;
+        }
+    }
+    return gt_wire_binding_result(err.c_str(), out, cap);
+}
+
+int gt_ext_pod_deleted(gt_ctx *c, const char *pod_uid)
+{
+    if (!c || !pod_uid) return GT_ERR_INVALID;
+    c->pod_request.erase(pod_uid);
+    auto it = c->pod_bound.find(pod_uid);
+    if (it == c->pod_bound.end()) return fail(c, GT_ERR_STATE, "gt_ext_pod_deleted: no GPUs recorded for pod %s", pod_uid);
+    const uint32_t node = it->second.first;
+    const uint16_t mask = it->second.second;
+    c->pod_bound.erase(it);
+    return gt_release(c, &node, &mask, 1);
 }
 
 int gt_synth_events(int config, uint64_t seed, uint32_t n_events, uint8_t *ev_k, uint32_t *ev_arg)

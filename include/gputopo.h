@@ -183,6 +183,42 @@ int gt_ext_bind(gt_ctx *ctx, uint32_t node, uint32_t m, int64_t assume_time, uin
 int gt_plugin_allocate(const char *pod_annotations, int64_t now, char *out_env, size_t env_cap,
                        char *out_annotations, size_t ann_cap);
 
+/* ---- the extender's HTTP bodies ---- */
+/* The request and reply types are upstream Kubernetes scheduler-extender types the reference links to
+ * (design.md:121) and does not contain: ExtenderArgs{Pod, Nodes, NodeNames} -> HostPriorityList [{Host, Score}] for
+ * `sort`, ExtenderBindingArgs{PodName, PodNamespace, PodUID, Node} -> ExtenderBindingResult{Error} for `bind`.
+ * Field names are matched without regard to case, as Go's encoding/json does.  With these a Go handler is
+ * `body -> C.gt_ext_sort_json -> w.Write`. */
+#define GT_RESOURCE_NAME "aliyun.com/gpu" /* managedResources name, design.md:102-108 */
+/* host only.  out_gpu_count: sum over the pod's containers of resources.limits[GT_RESOURCE_NAME] (requests where a
+ * container states no limit); a fractional or negative quantity is GT_ERR_PARSE (Gaia's Fragment case, 0 < m < 1,
+ * is not served: gaia.md:36).  out_uid: pod metadata.uid.  out_names: the NodeNames joined by '\n';
+ * out_n_names = -1 when the field is absent or null (= every node).  Buffers may be NULL; too small: GT_ERR_RANGE. */
+int gt_wire_parse_extender_args(const char *json, size_t len, uint32_t *out_gpu_count, char *out_uid, size_t uid_cap,
+                                char *out_names, size_t names_cap, int32_t *out_n_names);
+/* host only.  names: n node names separated by '\n'; scores: n bytes -> [{"Host":"a","Score":7},...] */
+int gt_wire_host_priorities(const char *names, uint32_t n, const uint8_t *scores, char *out, size_t cap,
+                            size_t *out_len);
+int gt_wire_parse_binding_args(const char *json, size_t len, char *out_pod_name, size_t name_cap,
+                               char *out_pod_namespace, size_t ns_cap, char *out_pod_uid, size_t uid_cap,
+                               char *out_node, size_t node_cap);
+int gt_wire_binding_result(const char *error, char *out, size_t cap);
+/* node names in node-index order, separated by '\n' (what the informer knows the nodes as): needed by the two
+ * handlers below.  count must equal the number of loaded nodes when they are called. */
+int gt_set_node_names(gt_ctx *ctx, const char *names, size_t len);
+/* replaces: the whole `sort` handler (design.md:99,117-118): ExtenderArgs JSON in, HostPriorityList JSON out
+ * (scores for the NodeNames of the request in their order, or for every node).  Remembers the pod's GPU count by
+ * its uid for the bind that follows.  Unknown node names score 0. */
+int gt_ext_sort_json(gt_ctx *ctx, const char *request, size_t len, char *out, size_t cap, size_t *out_len);
+/* replaces: the whole `bind` handler (design.md:100,119,223-234): ExtenderBindingArgs JSON in; picks the GPUs for the
+ * pod seen by the last gt_ext_sort_json with that uid, commits them, records pod -> (node, GPUs) and returns the
+ * ExtenderBindingResult JSON (Error set for an unknown pod / node or when the node cannot serve the request; the
+ * return code is GT_OK whenever a reply body was produced) plus the pod annotations of design.md:229-231. */
+int gt_ext_bind_json(gt_ctx *ctx, const char *request, size_t len, int64_t assume_time, char *out, size_t cap,
+                     char *out_annotations, size_t ann_cap);
+/* pod deletion seen by the informer: releases the GPUs gt_ext_bind_json recorded for the uid (GT_ERR_STATE: unknown) */
+int gt_ext_pod_deleted(gt_ctx *ctx, const char *pod_uid);
+
 /* ---- asynchronous / measurement surface ---- */
 int gt_score_all_async(gt_ctx *ctx);     /* enqueue scoring + cluster argmin, no copies, no sync */
 int gt_sync(gt_ctx *ctx);
