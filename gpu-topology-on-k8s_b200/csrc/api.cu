@@ -999,8 +999,13 @@ int setup_peer_exchange(gt_ctx *c)
     const size_t inbox_words = (size_t)world * 32 + (size_t)world * 2;
     cudaIpcMemHandle_t mine;
     memset(&mine, 0, sizeof mine);
-    unsigned char *d_handles = nullptr;
-    unsigned long long *d_ok = nullptr;
+    struct Scratch {       // set-up buffers: freed on every way out
+        unsigned char *handles = nullptr;
+        unsigned long long *ok = nullptr;
+        ~Scratch() { cudaFree(handles); cudaFree(ok); }
+    } tmp;
+    unsigned char *&d_handles = tmp.handles;
+    unsigned long long *&d_ok = tmp.ok;
     std::vector<cudaIpcMemHandle_t> all((size_t)world);
     GT_CUDA(c, cudaMalloc(&d_handles, (size_t)(world + 1) * sizeof(cudaIpcMemHandle_t)));
     GT_CUDA(c, cudaMalloc(&d_ok, sizeof(unsigned long long)));
@@ -1035,8 +1040,6 @@ int setup_peer_exchange(gt_ctx *c)
     if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     GT_CUDA(c, cudaMemcpy(&ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost));
-    cudaFree(d_handles);
-    cudaFree(d_ok);
     c->p2p = ok != 0;
     if (!c->p2p) return GT_OK;
     // one exchange now: first touch of the peer mappings happens before any timed pass
@@ -1067,6 +1070,7 @@ int gt_comm_unique_id(uint8_t out_id[128])
 int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
 {
     if (!c || !id || world < 1 || rank < 0 || rank >= world) return GT_ERR_INVALID;
+    if (c->comm) return fail(c, GT_ERR_STATE, "gt_comm_init: the context already has a communicator%s");
     NcclApi *api = nccl_api();
     if (!api) return fail(c, GT_ERR_NCCL, "libnccl.so.2 not loadable%s");
     GT_CUDA(c, cudaSetDevice(c->device));
