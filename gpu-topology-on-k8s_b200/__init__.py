@@ -31,6 +31,7 @@ EXPORTS = [
     "gt_tree_tables", "gt_load_trees", "gt_gaia_select", "gt_comm_mode",
     "gt_wire_parse_extender_args", "gt_wire_host_priorities", "gt_wire_parse_binding_args", "gt_wire_binding_result",
     "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
+    "gt_level_from_p2plink", "gt_levels_from_p2plink",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -128,6 +129,8 @@ def _lib():
     L.gt_load_trees.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(GtTree), u16p]
     L.gt_gaia_select.argtypes = [C.c_void_p, C.c_uint32, u32p]
     L.gt_comm_mode.argtypes = [C.c_void_p]
+    L.gt_level_from_p2plink.argtypes = [C.c_int32]
+    L.gt_levels_from_p2plink.argtypes = [C.POINTER(C.c_int32), C.c_uint32, u8p]
     L.gt_wire_parse_extender_args.argtypes = [C.c_char_p, C.c_size_t, u32p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
                                               C.POINTER(C.c_int32)]
     L.gt_wire_host_priorities.argtypes = [C.c_char_p, C.c_uint32, u8p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -473,6 +476,17 @@ EXTENDER_POLICY = {
     }],
 }
 RESOURCE_NAME = "aliyun.com/gpu"
+
+
+def levels_from_p2plink(types):
+    """n x n matrix of nvml.P2PLinkType values (the reference's gpuTopology map, design.md:57-70) -> levels[256]."""
+    t = np.ascontiguousarray(types, np.int32)
+    assert t.ndim == 2 and t.shape[0] == t.shape[1]
+    out = np.zeros(256, np.uint8)
+    rc = _lib().gt_levels_from_p2plink(t.ctypes.data_as(C.POINTER(C.c_int32)), t.shape[0], _p(out, u8p))
+    if rc:
+        raise GtError(rc, "gt_levels_from_p2plink")
+    return out
 
 
 def wire_parse_extender_args(body):

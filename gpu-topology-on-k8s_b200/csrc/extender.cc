@@ -153,6 +153,31 @@ int gt_parse_topo_matrix(const char *text, size_t len, uint8_t out_levels[256], 
     return GT_OK;
 }
 
+int gt_level_from_p2plink(int32_t p2p_link_type)
+{
+    // nvml.P2PLinkType of the Go bindings the design links to (design.md:50-52), in the order of the table of
+    // design.md:33-44 with P2PLinkUnknown = 0 in front; five and six NVLink links came later in the same enum
+    static const int8_t map[13] = {GT_LV_SYS /* unknown: assume the farthest */, GT_LV_SYS, GT_LV_NODE, GT_LV_PHB,
+                                   GT_LV_PXB, GT_LV_PIX, GT_LV_PSB, GT_LV_NV1, GT_LV_NV2, GT_LV_NV3, GT_LV_NV4,
+                                   GT_LV_NVS, GT_LV_NVS};
+    if (p2p_link_type < 0 || p2p_link_type > 12) return -1;
+    return map[p2p_link_type];
+}
+
+int gt_levels_from_p2plink(const int32_t *types, uint32_t n, uint8_t out_levels[256])
+{
+    if (!types || !out_levels || n < 1 || n > GT_MAX_GPUS) return GT_ERR_INVALID;
+    memset(out_levels, 0, 256);
+    for (uint32_t i = 0; i < n; i++)
+        for (uint32_t j = 0; j < n; j++) {
+            if (i == j) continue;                       // "gpu to itself is not recorded" design.md:19,73
+            const int code = gt_level_from_p2plink(types[i * n + j]);
+            if (code < 0) return GT_ERR_INVALID;
+            out_levels[i * 16 + j] = (uint8_t)code;
+        }
+    return GT_OK;
+}
+
 int gt_annotation_encode(const uint8_t levels[256], uint32_t n_gpus, char *out, size_t cap, size_t *out_len)
 {
     if (!levels || !out || cap == 0 || n_gpus > GT_MAX_GPUS) return GT_ERR_INVALID;

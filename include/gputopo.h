@@ -163,6 +163,14 @@ int gt_gaia_select(gt_ctx *ctx, uint32_t m, uint32_t *out_best);
 /* replaces: topology discovery output design.md:27-29 -- the `nvidia-smi topo -m` table
  * (imgs/gpu_topology_on_machine.png) -> 16x16 level codes.  NV# with # > 4 maps to GT_LV_NVS. */
 int gt_parse_topo_matrix(const char *text, size_t len, uint8_t out_levels[256], uint32_t *out_n);
+/* replaces: filling `type gpuTopology map[uint]map[uint]gpuTopologyType` (gpuTopologyType = nvml.P2PLinkType,
+ * design.md:57-70) -- the numeric enum of the NVML Go bindings the design links to (design.md:50-52; the bindings are
+ * not in the reference and no version is pinned): 0 unknown, then the rows of the table of design.md:33-44 in order,
+ * 1 cross CPU .. 6 same board, 7..10 one to four NVLink links; 11 and 12 (five, six links) -> GT_LV_NVS; unknown is
+ * taken as the farthest level (SYS).  types: n x n row-major, the diagonal is ignored.  Returns the GT_LV_* code,
+ * -1 / GT_ERR_INVALID for a value outside the enum. */
+int gt_level_from_p2plink(int32_t p2p_link_type);
+int gt_levels_from_p2plink(const int32_t *types, uint32_t n, uint8_t out_levels[256]);
 /* replaces: node annotations "GPU_<ABBR>_<i>_<j>: <description>" design.md:78-82 (one line per pair i<j) */
 int gt_annotation_encode(const uint8_t levels[256], uint32_t n_gpus, char *out, size_t cap, size_t *out_len);
 int gt_annotation_decode(const char *text, size_t len, uint8_t out_levels[256], uint32_t *out_n);

@@ -41,6 +41,27 @@ def test_parser_details(gt):
         gt.parse_topo_matrix(wide)
 
 
+def test_p2plink_enum_matrix_equals_parsed_text(gt, oracle):
+    """The reference keeps `gpuTopology map[uint]map[uint]nvml.P2PLinkType` (design.md:57-70): the same machine read as
+    that numeric enum and as `nvidia-smi topo -m` text gives the same level codes."""
+    enum = {"SYS": 1, "NODE": 2, "PHB": 3, "PXB": 4, "PIX": 5, "PSB": 6, "NV1": 7, "NV2": 8, "NV3": 9, "NV4": 10}
+    for name, want in enum.items():          # the rows of the table of design.md:33-44, in order
+        assert gt._lib().gt_level_from_p2plink(want) == gt.LV[name]
+    assert gt._lib().gt_level_from_p2plink(0) == gt.LV["SYS"]       # unknown: assume the farthest
+    assert gt._lib().gt_level_from_p2plink(11) == gt.LV["NVS"] and gt._lib().gt_level_from_p2plink(12) == gt.LV["NVS"]
+    assert gt._lib().gt_level_from_p2plink(13) == -1 and gt._lib().gt_level_from_p2plink(-1) == -1
+    for fx in ("f1_ring", "dgx1", "f2_pcie", "f3_tree4"):
+        text = open(os.path.join(GOLD, fx + ".topo.txt")).read()
+        lv, n = gt.parse_topo_matrix(text)
+        rows = [l.split() for l in text.splitlines() if l.split() and l.split()[0].startswith("GPU") and len(l.split()) > n]
+        rows = [r for r in rows if r[1] != "GPU1"][:n]
+        types = np.array([[0 if t == "X" else enum[t] for t in r[1:1 + n]] for r in rows], np.int32)
+        assert (gt.levels_from_p2plink(types) == lv).all()
+    with pytest.raises(gt.GtError):
+        gt.levels_from_p2plink(np.full((2, 2), 99, np.int32))
+    assert (gt.levels_from_p2plink(np.array([[99]], np.int32)) == 0).all()      # the diagonal is never read
+
+
 def test_node_annotation_codec(gt, oracle):
     # design.md:80: "GPU_SYS_0_1: Cross CPU socket"
     lv = np.zeros(256, np.uint8)
