@@ -17,7 +17,7 @@ INFEASIBLE = 0xFFFF0000
 NO_PLACE = 0xFFFFFFFFFFFFFFFF
 LV = dict(X=0, NVS=1, NV4=2, NV3=3, NV2=4, NV1=5, PSB=6, PIX=7, PXB=8, PHB=9, NODE=10, SYS=11)
 LUT_DEFAULT, LUT_DESIGN_MARKS = 0, 1
-K1_FIRST_UNUSED, K1_GAIA_SINGULAR = 0, 1
+K1_FIRST_UNUSED, K1_GAIA_SINGULAR, K1_FARTHEST = 0, 1, 2
 FLAG_GRAPH, FLAG_NO_MEMO, FLAG_MEMO_PASS = 2, 4, 8
 
 EXPORTS = [

@@ -304,9 +304,10 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
 // request-size-1 policy of the Gaia paper, applied after K1 (no-op for the default policy)
 int launch_singular(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *place)
 {
-    if (c->k1_policy != GT_K1_GAIA_SINGULAR || !n) return GT_OK;
+    if (c->k1_policy == GT_K1_FIRST_UNUSED || !n) return GT_OK;
     gt::k_singular<<<(n + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-        c->d_ngpus, c->d_free, c->d_access, c->d_sibling, d_ids, n, c->d_best, place, c->first_node);
+        c->d_ngpus, c->d_free, c->d_access, c->d_sibling, c->d_cost, c->k1_policy, d_ids, n, c->d_best, place,
+        c->first_node);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     return GT_OK;
@@ -388,7 +389,7 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
         c->step_nodes = c->n_nodes;
     }
     GT_CUDA(c, cudaGraphLaunch(c->step_exec[parity], c->stream));
-    c->launches += c->k1_policy == GT_K1_GAIA_SINGULAR ? 3 : 2;
+    c->launches += c->k1_policy != GT_K1_FIRST_UNUSED ? 3 : 2;
     c->place_cur = bin_place(c, parity);
     return GT_OK;
 }
@@ -454,7 +455,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     const bool memo_pass = !d_ids && n && (c->flags & GT_FLAG_MEMO_PASS) && !c->memo_pass_failed;
     const bool graph = !d_ids && n && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed;
     // plain K0 -> K1 pass with peers: all cross-stream ordering through device flags (see exchange_min)
-    bool flagged = c->comm && c->p2p && !d_ids && n && !memo_pass && !graph && c->k1_policy != GT_K1_GAIA_SINGULAR;
+    bool flagged = c->comm && c->p2p && !d_ids && n && !memo_pass && !graph && c->k1_policy == GT_K1_FIRST_UNUSED;
     if ((rc = wait_place_free(c, par, flagged)) != GT_OK) return rc;
     if (!d_ids && n) {
         bool done = false;
@@ -518,6 +519,7 @@ const char *gt_last_error(const gt_ctx *ctx) { return ctx ? ctx->err : ""; }
 int gt_create(const gt_config *cfg, gt_ctx **out)
 {
     if (!cfg || !out || cfg->struct_size < sizeof(gt_config) || cfg->max_nodes == 0) return GT_ERR_INVALID;
+    if (cfg->k1_policy > GT_K1_FARTHEST) return GT_ERR_INVALID;
     *out = nullptr;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {

@@ -765,14 +765,19 @@ __global__ void __launch_bounds__(kCta) k_int32_peak(uint32_t *out, uint32_t ite
     if (r == 0x12345678u) out[0] = r;
 }
 
-// ---------------------------------------------------------------- Gaia Alg. 3 "Singular" for request size 1
-// gpu_scheduler_algorithm_1.png: candidates = free GPUs that have siblings and whose siblings are all used;
-// lowest access cost (then lowest id) wins; without candidates the free GPU with the lowest access cost.
+// ---------------------------------------------------------------- request-size-1 policies beside "first unused"
+// policy 1, Gaia Alg. 3 "Singular" (gpu_scheduler_algorithm_1.png): candidates = free GPUs that have siblings and whose
+// siblings are all used; lowest access cost (then lowest id) wins; without candidates the free GPU with the lowest
+// access cost.
+// policy 2, the prose of design.md:135-147: the free GPU "far away from the GPU group" -- the largest pair-cost sum
+// to all GPUs of the node (a row sum of the symmetric, zero-diagonal cost tile), lowest id on ties (the CPU-affinity
+// tie-break of design.md:144-145 needs an input this path does not have).
 // Overrides best[node][0] (cost stays 0) and, for the node that holds the k = 1 placement key, its mask.
 __global__ void __launch_bounds__(kCta) k_singular(const uint8_t *__restrict__ n_gpus,
                                                    const uint16_t *__restrict__ free_mask,
                                                    const uint8_t *__restrict__ access,
                                                    const uint16_t *__restrict__ sibling,
+                                                   const uint8_t *__restrict__ cost, uint32_t policy,
                                                    const uint32_t *__restrict__ ids, uint32_t n,
                                                    uint32_t *__restrict__ best, unsigned long long *place,
                                                    uint32_t first_node)
@@ -785,12 +790,24 @@ __global__ void __launch_bounds__(kCta) k_singular(const uint8_t *__restrict__ n
     const uint32_t f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
     if (!f) return;
     int pick = -1, pick_any = -1;
-    uint32_t cost = 0xFFFFFFFFu, cost_any = 0xFFFFFFFFu;
-    for (uint32_t r = f; r; r &= r - 1) {
-        const int g = __ffs(r) - 1;
-        const uint32_t ac = access[(size_t)node * 16 + g], sib = sibling[(size_t)node * 16 + g];
-        if (ac < cost_any) { cost_any = ac; pick_any = g; }
-        if (sib != 0 && (sib & f) == 0 && ac < cost) { cost = ac; pick = g; }
+    if (policy == 2u) {
+        uint32_t far = 0;
+        for (uint32_t r = f; r; r &= r - 1) {
+            const int g = __ffs(r) - 1;
+            const uint4 row = __ldg(reinterpret_cast<const uint4 *>(cost + (size_t)node * 256 + g * 16));
+            const uint32_t w[4] = {row.x, row.y, row.z, row.w};
+            uint32_t sum = 0;
+            for (uint32_t j = 0; j < ng; j++) sum += (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+            if (pick < 0 || sum > far) { far = sum; pick = g; }
+        }
+    } else {
+        uint32_t c1 = 0xFFFFFFFFu, c_any = 0xFFFFFFFFu;
+        for (uint32_t r = f; r; r &= r - 1) {
+            const int g = __ffs(r) - 1;
+            const uint32_t ac = access[(size_t)node * 16 + g], sib = sibling[(size_t)node * 16 + g];
+            if (ac < c_any) { c_any = ac; pick_any = g; }
+            if (sib != 0 && (sib & f) == 0 && ac < c1) { c1 = ac; pick = g; }
+        }
     }
     const uint32_t v = 1u << (pick >= 0 ? pick : pick_any);
     best[(size_t)node * 16] = v;

@@ -55,7 +55,11 @@ enum {
     GT_LV_PSB = 6, GT_LV_PIX = 7, GT_LV_PXB = 8, GT_LV_PHB = 9, GT_LV_NODE = 10, GT_LV_SYS = 11
 };
 enum { GT_LUT_DEFAULT = 0, GT_LUT_DESIGN_MARKS = 1 };
-enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1 };
+/* request-size-1 policy (the reference gives three): the pseudo-code of design.md:154-160 (first unused
+ * device; what the exhaustive path yields by itself), Gaia Alg. 3 Singular, and the prose of design.md:135-147 (the unused
+ * GPU farthest from the GPU group: largest distance sum to all GPUs of the node; lowest id on ties -- the CPU-affinity
+ * tie-break of design.md:144-145 needs an input this path does not have) */
+enum { GT_K1_FIRST_UNUSED = 0, GT_K1_GAIA_SINGULAR = 1, GT_K1_FARTHEST = 2 };
 enum { GT_FLAG_GRAPH = 2 /* replay K0 -> K1 as a captured CUDA graph instead of two plain launches (measured slower) */,
        GT_FLAG_NO_MEMO = 4 /* gt_schedule re-scores on the GPU per event instead of using the memo table */,
        GT_FLAG_MEMO_PASS = 8 /* full passes copy rows out of the GPU-built (topology class, free mask) table instead of
@@ -68,7 +72,7 @@ typedef struct gt_config {
     int32_t device;        /* CUDA device ordinal */
     uint32_t max_nodes;    /* capacity of this context (its shard of the cluster) */
     uint32_t first_node;   /* global index of local node 0: placement keys carry first_node + local */
-    uint32_t k1_policy;    /* GT_K1_*: design.md:154-160 first unused device, or Gaia Alg. 3 */
+    uint32_t k1_policy;    /* GT_K1_* */
     uint32_t flags;        /* GT_FLAG_* */
     void *stream;          /* optional cudaStream_t to launch on; NULL = the library creates one */
 } gt_config;

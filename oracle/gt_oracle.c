@@ -199,6 +199,21 @@ uint64_t gto_greedy_cluster(const uint8_t *levels, const uint8_t *n_gpus, const 
 
 /* ------------------------------------------------------------------ Gaia Alg. 3 / 4 / 1 */
 
+/* design.md:135-147 */
+int gto_k1_farthest(const uint8_t levels[256], int n_gpus, uint16_t free_mask, const uint8_t lut[16])
+{
+    int i, j, best = -1; uint32_t best_sum = 0;
+    if (n_gpus > GTO_MAX_GPUS) n_gpus = GTO_MAX_GPUS;
+    for (i = 0; i < n_gpus; i++) {
+        uint32_t sum = 0;
+        if (!((free_mask >> i) & 1)) continue;                    /* "if gpu not used" */
+        for (j = 0; j < n_gpus; j++)                              /* distance to all GPUs, upper-triangle entry */
+            if (j != i) sum += lut[levels[(i < j ? i : j) * 16 + (i < j ? j : i)] & 15];
+        if (best < 0 || sum > best_sum) { best = i; best_sum = sum; }   /* the longest path sum; first on ties */
+    }
+    return best;
+}
+
 /* gpu_scheduler_algorithm_1.png lines 1-10 */
 int gto_gaia_singular(int n_gpus, uint16_t free_mask, const uint8_t access_cost[16],
                       const uint16_t sibling_mask[16])

@@ -72,6 +72,11 @@ uint16_t gto_greedy_node(const uint8_t levels[256], int n_gpus, uint16_t free_ma
 uint64_t gto_greedy_cluster(const uint8_t *levels, const uint8_t *n_gpus, const uint16_t *free_mask,
                             uint32_t n_nodes, const uint8_t lut[16], uint32_t *out_best);
 
+/* design.md:135-147, the prose variant for request size 1: the unused GPU "far away from the GPU group" -- the one
+ * whose distance sum to ALL GPUs of the node is largest; the CPU-affinity tie-break of design.md:144-145 needs an input
+ * this path does not have, ties go to the lowest id.  Returns gpu id or -1. */
+int gto_k1_farthest(const uint8_t levels[256], int n_gpus, uint16_t free_mask, const uint8_t lut[16]);
+
 /* Gaia Alg. 3 Singular (m == 1): candidates = free GPU whose siblings ("cousin") are all used
  * (and that has at least one sibling); lowest access cost, then lowest id; if none, the free GPU
  * with lowest access cost.  Returns gpu id or -1. */

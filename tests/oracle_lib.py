@@ -96,6 +96,9 @@ class Oracle:
     def gaia_singular(self, n, free, access_cost, sibling_mask):
         return int(self.lib.gto_gaia_singular(C.c_int(n), C.c_uint16(free), _p(access_cost, u8p), _p(sibling_mask, u16p)))
 
+    def k1_farthest(self, levels, n, free, lut):
+        return int(self.lib.gto_k1_farthest(_p(levels, u8p), C.c_int(n), C.c_uint16(int(free)), _p(lut, u8p)))
+
     def gaia_link(self, tree, free, m):
         return int(self.lib.gto_gaia_link(C.byref(tree), C.c_uint16(free), C.c_int(m)))
 

@@ -351,6 +351,57 @@ def test_gaia_singular_policy_on_device(gt, oracle):
         assert placed == 1 and int(on[0]) == 0 and int(om[0]) in (4, 8)
 
 
+def test_farthest_policy_on_device(gt, oracle):
+    """GT_K1_FARTHEST: request size 1 follows the prose of design.md:135-147 (the unused GPU with the largest distance
+    sum to all GPUs of the node); every other request size is unchanged; dirty path, placement key and commit loop
+    keep the policy."""
+    lut = oracle.lut(0)
+    for cls in ("F2_PCIE", "F3_TREE4", "DGX1", "F1_RING"):
+        lv, n, _, _ = oracle.class_topology(ol.CLS[cls])
+        N = 1 << n
+        levels = np.tile(lv, (N, 1))
+        free = np.arange(N, dtype=np.uint16)
+        with gt.Allocator(N, k1_policy=gt.K1_FARTHEST) as a:
+            a.load_nodes(levels, np.full(N, n, np.uint8), free)
+            got = a.score_all()
+            want, _ = oracle.exhaustive_cluster(levels, np.full(N, n, np.uint8), free, lut, 4)
+            for f in range(1, N):
+                want[f, 0] = 1 << oracle.k1_farthest(lv, n, f, lut)
+            assert (got == want).all()
+            place = a.best_node([1, 2])
+            assert gt.place_fields(place[0]) == (0, 1, int(want[1, 0]) & 0xFFFF)
+            assert int(place[1]) == int(oracle.cluster_argmin(want)[1])
+            a.commit([N - 1], [1])
+            a.score_dirty()
+            want[N - 1] = want[N - 2]
+            assert (a.score_all() == want).all()
+    # F2 with everything free: GPU6 / GPU7 hang directly under the root, GPU6 is the farthest
+    lv, n, _, _ = oracle.class_topology(ol.CLS["F2_PCIE"])
+    with gt.Allocator(2, k1_policy=gt.K1_FARTHEST) as a:
+        a.load_nodes(np.tile(lv, (2, 1)), [8, 8], [0xFF, 0xFF])
+        a.score_all()
+        assert a.allocate(0, 1)[0] == 1 << 6
+        placed, on, om = a.schedule(np.array([1, 1], np.uint8), np.array([0, 0], np.uint32))
+        assert placed == 2 and list(on) == [0, 0] and [int(m) for m in om] == [1 << 6, 1 << 7]
+    # random matrices, cost tables and GPU counts
+    rng = np.random.RandomState(77)
+    N = 700
+    levels = rng.randint(1, 16, (N, 256)).astype(np.uint8)
+    ngs = rng.randint(1, 17, N).astype(np.uint8)
+    free = rng.randint(0, 1 << 16, N).astype(np.uint16)
+    rl = rng.randint(0, 256, 16).astype(np.uint8)
+    with gt.Allocator(N, k1_policy=gt.K1_FARTHEST) as a:
+        a.set_cost_lut(rl)
+        a.load_nodes(levels, ngs, free)
+        got = a.score_all()
+        want, _ = oracle.exhaustive_cluster(levels, ngs, free, rl, 4)
+        for i in range(N):
+            g = oracle.k1_farthest(levels[i], int(ngs[i]), int(free[i]) & ((1 << int(ngs[i])) - 1), rl)
+            if g >= 0:
+                want[i, 0] = 1 << g
+        assert (got == want).all()
+
+
 def test_split_units_and_high_positions(gt, oracle):
     """Shapes the work decomposition treats specially: many nodes with >= 14 free GPUs (a node spans several
     warp units whose minima meet through atomics), 16-GPU nodes with <= 8 free GPUs at high indices, the maximum

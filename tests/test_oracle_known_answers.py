@@ -202,6 +202,30 @@ def test_greedy_cluster_is_the_per_node_greedy(oracle):
             assert int(out[i, m - 1]) == (gc << 16) | g
 
 
+def test_k1_farthest_prose_policy(oracle):
+    """design.md:135-147: the unused GPU with the largest distance sum to all GPUs; lowest id on ties."""
+    lut = oracle.lut(0)
+    lv, n, _, _ = oracle.class_topology(ol.CLS["F2_PCIE"])
+    assert oracle.k1_farthest(lv, n, 0xFF, lut) == 6          # GPU6/7 sit alone under the root (SOC to everything else)
+    assert oracle.k1_farthest(lv, n, 0xFF & ~(1 << 6), lut) == 7
+    assert oracle.k1_farthest(lv, n, 0x0F, lut) == 2          # among 0..3: GPU2/3 (PXB to 0,1) are farther than 0/1 (PIX)
+    assert oracle.k1_farthest(lv, n, 0, lut) == -1
+    rng = np.random.RandomState(2)
+    for _ in range(300):
+        n = int(rng.randint(1, 17))
+        lvr = rng.randint(1, 16, 256).astype(np.uint8)
+        rl = rng.randint(0, 256, 16).astype(np.uint8)
+        f = int(rng.randint(0, 1 << n))
+        g = oracle.k1_farthest(lvr, n, f, rl)
+        m = lvr.reshape(16, 16)
+        sums = {i: sum(int(rl[m[min(i, j), max(i, j)] & 15]) for j in range(n) if j != i) for i in range(n) if (f >> i) & 1}
+        if not sums:
+            assert g == -1
+        else:
+            top = max(sums.values())
+            assert g == min(i for i, v in sums.items() if v == top)
+
+
 def test_gaia_link_matches_exhaustive_on_trees(oracle):
     """Cross-check: on tree-shaped topologies with all GPUs free Alg. 4 is cost-optimal."""
     lut = oracle.lut(0)
