@@ -80,3 +80,20 @@ def test_synth_events_match_oracle(gt, oracle, config, seed):
         assert abs((k > 0).mean() - 0.55) < 0.02
     else:
         assert (k > 0).all() and k.max() == 8 and k.min() == 1
+
+
+def test_host_parsers_survive_fuzzing_under_sanitizers(tmp_path):
+    """The text / JSON parsers take bytes from the network (extender bodies, annotations): tools/fuzz_host.cc mutates
+    valid inputs and feeds random trees to every host-only entry point under ASan + UBSan."""
+    import subprocess
+    csrc = os.path.join(ROOT, "gpu-topology-on-k8s_b200", "csrc")
+    exe = str(tmp_path / "fuzz_host")
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+           "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tools", "fuzz_host.cc")] + \
+          [os.path.join(csrc, f) for f in ("extender.cc", "wire.cc", "gaia_tree.cc", "host.cc")] + ["-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0 and "sanitize" in r.stderr:
+        pytest.skip("no sanitizer runtime in this toolchain")
+    assert r.returncode == 0, r.stderr[-2000:]
+    r = subprocess.run([exe, "20000"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "no sanitizer report" in r.stdout, r.stdout[-1000:] + r.stderr[-3000:]
