@@ -9,7 +9,8 @@
  * a design document and no allocator source, so there is nothing to compile
  * under oracle/_ref.  This file is a plain-C restatement of the algorithms the reference documents
  * describe, pinned by the six known answers those documents contain (SURVEY.md section 4, KA1-KA6;
- * tests/test_oracle_known_answers.py).
+ * tests/test_oracle_known_answers.py) and by the greedy-vs-exhaustive divergence counts an independent script
+ * produced for that survey (18 / 86 costlier, 28 / 30 equal-cost-different choices of 769 on F1 / DGX-1).
  *
  * Citations: design.md:N = /root/reference/design.md line N; "Alg. 1/3/4" = the Gaia paper
  * algorithms reproduced in /root/reference/reference/gaia_gpu_topology/gpu_scheduler_algorithm*.{jpg,png}.
