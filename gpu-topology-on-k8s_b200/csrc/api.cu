@@ -333,7 +333,9 @@ int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity, bool fla
         for (int q = 0; q < c->world; q++) prm.inbox[q] = c->peer_inbox[q];
         prm.done_flag = c->d_xflags + 1 + parity;
         prm.seq = ++c->xchg_seq;
-        prm.rank = (uint32_t)c->rank; prm.world = (uint32_t)c->world; prm.parity = parity;
+        // inbox slots alternate with the exchange number, which every rank counts alike; the local key-buffer parity
+        // may drift between ranks (a rank-local gt_time_kernel runs passes the others do not)
+        prm.rank = (uint32_t)c->rank; prm.world = (uint32_t)c->world; prm.parity = (uint32_t)(prm.seq & 1u);
         gt::k_exchange<<<1, 16 * gt::kMaxPeers, 0, c->comm_stream>>>(prm);
         c->launches++;
         GT_CUDA(c, cudaGetLastError());

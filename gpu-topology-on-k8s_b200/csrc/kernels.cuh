@@ -594,7 +594,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 // until all flags of its own inbox carry that number and reduces the world x 16 keys with min -- one store and one
 // flag round trip over NVLink, no host involvement and nothing in front of the next pass on the scoring stream:
 // the kernel can be enqueued before K1 has run and waits for K1's `seq_flag` itself.
-// Inbox (u64 words): keys[world][2 parities][16], then flags[world][2].  Parities alternate between passes, and a
+// Inbox (u64 words): keys[world][2 parities][16], then flags[world][2].  Parities alternate with the exchange number, and a
 // rank reuses a parity only after its previous exchange on the other parity completed, i.e. after every peer has
 // entered that one -- by stream order the peers have then finished reading this parity.
 constexpr int kMaxPeers = 8;
