@@ -31,7 +31,7 @@ EXPORTS = [
     "gt_tree_tables", "gt_load_trees", "gt_gaia_select", "gt_comm_mode",
     "gt_wire_parse_extender_args", "gt_wire_host_priorities", "gt_wire_parse_binding_args", "gt_wire_binding_result",
     "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
-    "gt_level_from_p2plink", "gt_levels_from_p2plink",
+    "gt_level_from_p2plink", "gt_levels_from_p2plink", "gt_lut_cmax",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -121,6 +121,8 @@ def _lib():
     L.gt_destroy.restype = None
     L.gt_set_cost_lut.argtypes = [C.c_void_p, u8p]
     L.gt_lut_preset.argtypes = [C.c_int, u8p]
+    L.gt_lut_cmax.argtypes = [u8p]
+    L.gt_lut_cmax.restype = C.c_uint32
     for f in ("gt_score_int", "gt_score_milli"):
         getattr(L, f).argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     L.gt_load_nodes.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, u8p, u8p, u8p, u16p, u16p]
@@ -188,6 +190,11 @@ def lut_preset(preset=LUT_DEFAULT):
     if rc:
         raise GtError(rc, "gt_lut_preset")
     return out
+
+
+def lut_cmax(lut):
+    """The normaliser of the score formula: largest cost over the link kinds of the table (codes 1..SYS)."""
+    return int(_lib().gt_lut_cmax(_p(np.ascontiguousarray(lut, np.uint8), u8p)))
 
 
 def score_int(s, length, cmax):

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <mutex>
 #include <new>
 #include <string>
@@ -94,6 +95,7 @@ struct gt_ctx {
     std::vector<std::string> node_names;
     std::unordered_map<std::string, uint32_t> node_index;
     std::unordered_map<std::string, uint32_t> pod_request;                       // uid -> GPUs asked for (from sort)
+    std::deque<std::string> pod_request_order;                                   // oldest first: the table is bounded
     std::unordered_map<std::string, std::pair<uint32_t, uint16_t>> pod_bound;    // uid -> (node, GPUs)
     unsigned long long *d_inbox = nullptr;      // own inbox: keys[world][2][16] + flags[world][2]
     unsigned long long *peer_inbox[gt::kMaxPeers] = {};
@@ -779,22 +781,30 @@ int gt_commit(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t 
     if (!c || !nodes || !masks) return GT_ERR_INVALID;
     for (uint32_t i = 0; i < count; i++) {
         if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_commit: node id out of range%s");
-        if ((c->h_free[nodes[i]] & masks[i]) != masks[i]) return fail(c, GT_ERR_STATE, "gt_commit: GPU already in use%s");
+        if (masks[i] & ~((1u << c->h_ngpus[nodes[i]]) - 1u)) return fail(c, GT_ERR_INVALID, "gt_commit: GPU index beyond the node's GPU count%s");
     }
     int rcw = mirror_writable(c);
     if (rcw != GT_OK) return rcw;
+    // entries are checked against the masks as the earlier entries of this batch left them: the same GPU cannot be
+    // handed out twice by one call; on a conflict the batch is undone
     for (uint32_t i = 0; i < count; i++) {
+        if ((c->h_free[nodes[i]] & masks[i]) != masks[i]) {
+            for (uint32_t j = 0; j < i; j++) c->h_free[nodes[j]] |= masks[j];
+            return fail(c, GT_ERR_STATE, "gt_commit: GPU already in use%s");
+        }
         c->h_free[nodes[i]] &= (uint16_t)~masks[i];
-        mark_dirty(c, nodes[i]);
     }
+    for (uint32_t i = 0; i < count; i++) mark_dirty(c, nodes[i]);
     return GT_OK;
 }
 
 int gt_release(gt_ctx *c, const uint32_t *nodes, const uint16_t *masks, uint32_t count)
 {
     if (!c || !nodes || !masks) return GT_ERR_INVALID;
-    for (uint32_t i = 0; i < count; i++)
+    for (uint32_t i = 0; i < count; i++) {
         if (nodes[i] >= c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_release: node id out of range%s");
+        if (masks[i] & ~((1u << c->h_ngpus[nodes[i]]) - 1u)) return fail(c, GT_ERR_INVALID, "gt_release: GPU index beyond the node's GPU count%s");
+    }
     int rcw = mirror_writable(c);
     if (rcw != GT_OK) return rcw;
     for (uint32_t i = 0; i < count; i++) {
@@ -1300,8 +1310,7 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     else if (!c->dirty.empty()) rc = gt_score_dirty(c);
     if (rc != GT_OK) return rc;
     if (!c->n_nodes) return GT_OK;
-    uint32_t cmax = 0;
-    for (int i = 1; i < 16; i++) cmax = std::max<uint32_t>(cmax, c->lut[i]);
+    const uint32_t cmax = gt_lut_cmax(c->lut);
     if (out_place && c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
     // the kernel stores scores and keys into mapped pinned memory: no device-to-host copy behind it
     const uint32_t threads = (c->n_nodes + 3) / 4;
@@ -1353,6 +1362,8 @@ int gt_set_node_names(gt_ctx *c, const char *names, size_t len)
     return GT_OK;
 }
 
+constexpr size_t kMaxPendingPods = 65536;   // pods seen by sort and not (yet) bound
+
 int gt_ext_sort_json(gt_ctx *c, const char *request, size_t len, char *out, size_t cap, size_t *out_len)
 {
     if (!c || !request || !out) return GT_ERR_INVALID;
@@ -1364,7 +1375,19 @@ int gt_ext_sort_json(gt_ctx *c, const char *request, size_t len, char *out, size
         return fail(c, GT_ERR_INVALID, "gt_ext_sort_json: the pod asks for no or more than 16 " GT_RESOURCE_NAME "%s");
     std::vector<uint8_t> scores(c->n_nodes ? c->n_nodes : 1);
     if ((rc = gt_ext_sort(c, a.gpu_count, scores.data(), nullptr)) != GT_OK) return rc;
-    if (!a.uid.empty()) c->pod_request[a.uid] = a.gpu_count;
+    if (!a.uid.empty()) {
+        // pods that were scored and then bound elsewhere, found unschedulable or re-submitted under a new uid never
+        // reach bind or pod_deleted: the table keeps the kMaxPendingPods most recent uids
+        if (c->pod_request.emplace(a.uid, a.gpu_count).second) {
+            c->pod_request_order.push_back(a.uid);
+            while (c->pod_request_order.size() > kMaxPendingPods) {
+                c->pod_request.erase(c->pod_request_order.front());   // no-op when bind already took it
+                c->pod_request_order.pop_front();
+            }
+        } else {
+            c->pod_request[a.uid] = a.gpu_count;
+        }
+    }
     std::string s = "[";
     auto item = [&](const std::string &name, unsigned score, bool first) {
         if (!first) s.push_back(',');
@@ -1474,6 +1497,9 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
                                      uint32_t n_nodes, uint32_t *d_best, void *stream, char *err_buf, size_t err_len)
 {
     if (err_buf && err_len) err_buf[0] = 0;
+#ifdef GT_TRACE
+    return static_fail(GT_ERR_STATE, err_buf, err_len, "trace build: gt_score_nodes_static is disabled");
+#endif
     if (n_nodes > GT_STATIC_MAX_NODES) {
         char d[96];
         snprintf(d, sizeof d, "%u nodes requested, the built-in scratch holds at most %u", n_nodes, GT_STATIC_MAX_NODES);
@@ -1514,13 +1540,20 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
         scratch = g_static_dev_ptr[dev];
         sms = g_static_sms[dev];
     }
-    cudaPointerAttributes attr;
-    e = cudaPointerGetAttributes(&attr, d_best);
-    if (e != cudaSuccess || (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged) ||
-        (attr.type == cudaMemoryTypeDevice && attr.device != dev)) {
-        cudaGetLastError();
-        return static_fail(GT_ERR_INVALID, err_buf, err_len,
-                           "gt_score_nodes_static: d_best is not device memory of the current device");
+    // a host pointer in any of the four would fault inside the kernels (or, where the GPU can reach host memory,
+    // quietly use the wrong bytes): refuse it here
+    const struct { const void *p; const char *name; } bufs[4] = {
+        {d_cost, "d_cost"}, {d_n_gpus, "d_n_gpus"}, {d_free_mask, "d_free_mask"}, {d_best, "d_best"}};
+    for (const auto &b : bufs) {
+        cudaPointerAttributes attr;
+        e = cudaPointerGetAttributes(&attr, b.p);
+        if (e != cudaSuccess || (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged) ||
+            (attr.type == cudaMemoryTypeDevice && attr.device != dev)) {
+            cudaGetLastError();
+            char d[96];
+            snprintf(d, sizeof d, "%s is not device memory of the current device", b.name);
+            return static_fail(GT_ERR_INVALID, err_buf, err_len, "gt_score_nodes_static: ", d);
+        }
     }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     uint32_t *cnt = scratch, *list = scratch + kStaticCntWords;
@@ -1536,9 +1569,6 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;
     prm.seq_flag = nullptr; prm.seq = 0;
-#ifdef GT_TRACE
-    return static_fail(GT_ERR_STATE, err_buf, err_len, "trace build: gt_score_nodes_static is disabled");
-#endif
     const uint32_t grid = std::min<uint32_t>(n_nodes / 8 + gt::kBins, (uint32_t)sms * gt::kScoreMinCtas);
     gt::k_score<<<grid, gt::kScoreCta, 0, s>>>(prm);
     e = cudaGetLastError();

@@ -121,6 +121,14 @@ int gt_lut_preset(int preset, uint8_t out_lut[16])
     return GT_ERR_INVALID;
 }
 
+uint32_t gt_lut_cmax(const uint8_t lut[16])
+{
+    uint32_t m = 0;
+    if (!lut) return 0;
+    for (int i = 1; i <= GT_LV_SYS; i++) m = lut[i] > m ? lut[i] : m;
+    return m;
+}
+
 int gt_score_milli(uint32_t sum, uint32_t len, uint32_t cmax)
 {
     const uint64_t den = (uint64_t)cmax * len;

@@ -154,8 +154,10 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 #endif
     if (place && blockIdx.x == 0 && tid < 16) {
         // multi-GPU: the exchange that last used this key buffer (two passes ago) must have finished with it
-        if (wait_flag)
+        if (wait_flag) {
             while (*reinterpret_cast<const volatile unsigned long long *>(wait_flag) < wait_val) __nanosleep(64);
+            __threadfence();   // acquire side of the exchange kernel's release (fence + flag store)
+        }
         place[tid] = ~0ull;
     }
     __syncthreads();
@@ -613,8 +615,10 @@ struct ExchangeParams {
 __global__ void __launch_bounds__(16 * kMaxPeers) k_exchange(ExchangeParams prm)
 {
     const uint32_t tid = threadIdx.x, k = tid & 15u, q = tid >> 4;
-    if (tid == 0 && prm.k1_flag)
+    if (tid == 0 && prm.k1_flag) {
         while (*reinterpret_cast<const volatile unsigned long long *>(prm.k1_flag) < prm.k1_val) __nanosleep(100);
+        __threadfence();   // acquire side of K1's release (folds, fence, flag store): the reads of `place` below stay behind it
+    }
     __syncthreads();
     const uint32_t slot = prm.rank * 2 + prm.parity;
     if (q < prm.world) {

@@ -89,6 +89,10 @@ int gt_lut_preset(int preset, uint8_t out_lut[16]);
 int gt_set_cost_lut(gt_ctx *ctx, const uint8_t lut[16]);
 /* replaces: score formula design.md:205-217.  floor(10*(cmax*len-sum)/(cmax*len)), len = C(k,2) */
 int gt_score_int(uint32_t sum, uint32_t len, uint32_t cmax);
+/* replaces: the "6" of design.md:208 -- the largest mark of the table: max of the cost table over the link kinds
+ * the table and the parsers know (codes 1..GT_LV_SYS).  User-defined codes 12..15 do not stretch the scale; a
+ * combination whose cost exceeds cmax*len scores 0.  This is what gt_ext_sort normalises by. */
+uint32_t gt_lut_cmax(const uint8_t lut[16]);
 int gt_score_milli(uint32_t sum, uint32_t len, uint32_t cmax);
 
 /* ---- topology tables ---- */
@@ -264,6 +268,14 @@ int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms
  *   - n_nodes <= GT_STATIC_MAX_NODES, otherwise GT_ERR_RANGE (and a message in err_buf, if given);
  *   - the device that owns the buffers must be current; the first call on each device looks up the
  *     array's device address (one-time set-up) and should therefore happen before any stream capture;
+ *   - that first call is also where the CUDA runtime loads this library's device code onto the GPU
+ *     (lazy module loading): the driver reserves the array and the kernel images then, and that step
+ *     CAN need device memory.  Make the first call per device at start-up, before a pool takes the
+ *     whole GPU (a call with n_nodes = 1 on dummy buffers will do), or run with
+ *     CUDA_MODULE_LOADING=EAGER so that the load happens when the library is opened.  Every later
+ *     call on that device reserves nothing (the test checks the free-memory figure across calls);
+ *   - all four buffers must be device (or managed) memory of the current device: host pointers are
+ *     refused with GT_ERR_INVALID before anything is launched;
  *   - all calls on a device share the one array: the counters are cleared at the start of every call,
  *     the rest is overwritten, but two calls that overlap on the GPU (different streams without an
  *     ordering between them, or several host threads) race -- keep them stream-ordered;

@@ -27,7 +27,8 @@ void gto_lut_preset(int preset, uint8_t lut[16])
 uint32_t gto_lut_cmax(const uint8_t lut[16])
 {
     uint32_t m = 0; int i;
-    for (i = 1; i < 16; i++) if (lut[i] > m) m = lut[i];
+    /* the marks of the table of design.md:196-203 (+ NVSwitch): codes 1..SYS; user-defined codes 12..15 stay out */
+    for (i = 1; i <= GTO_LV_SYS; i++) if (lut[i] > m) m = lut[i];
     return m;
 }
 

@@ -109,7 +109,7 @@ def test_codec_fuzz_against_python_json(gt):
 @pytest.mark.gpu
 def test_sort_and_bind_handlers_on_json_bodies(gt, oracle):
     lut = oracle.lut(0)
-    cmax = int(lut.max())
+    cmax = oracle.cmax(lut)
     N = 300
     lv, ng, fr, _ = oracle.synth_cluster(4, 0xE47, 0, N)
     names = ["node-%03d" % i for i in range(N)]

@@ -167,6 +167,31 @@ def test_commit_release_rescore_dirty(gt, oracle):
             a.commit([0], [0xFFFF])     # GPUs not free
 
 
+def test_commit_batch_is_checked_cumulatively(gt, oracle):
+    """One batch cannot hand the same GPU out twice, and a refused batch leaves no trace."""
+    lv, n, fr, _ = gt.synth_cluster(2, 0x5EED0002, 0, 8)
+    free = np.full(8, 0xFF, np.uint16)
+    with gt.Allocator(8) as a:
+        a.load_nodes(lv, n, free)
+        before = a.score_all()
+        with pytest.raises(gt.GtError) as e:
+            a.commit([3, 5, 3], [0x03, 0x10, 0x06])      # GPU 1 of node 3 twice
+        assert e.value.code == -8
+        with pytest.raises(gt.GtError) as e:
+            a.commit([2], [0x0100])                      # GPU 8 on an 8-GPU node
+        assert e.value.code == -1
+        with pytest.raises(gt.GtError):
+            a.release([2], [0x0100])
+        a.score_dirty()
+        assert (a.score_all() == before).all()
+        a.commit([3, 5, 3], [0x03, 0x10, 0x0C])          # disjoint: fine
+        free[3] &= ~0x0F & 0xFFFF
+        free[5] &= ~0x10 & 0xFFFF
+        a.score_dirty()
+        want, _ = oracle.exhaustive_cluster(lv, n, free, oracle.lut(0), 2)
+        assert (a.score_all() == want).all()
+
+
 def test_full_size_properties(gt, oracle):
     """BASELINE config 4 at its full 100 000 nodes: size-independent properties + a sampled oracle check."""
     N = 100000
