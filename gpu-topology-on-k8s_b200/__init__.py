@@ -110,7 +110,7 @@ def _lib():
     so = os.environ.get("GT_LIB")      # profiling aid: load another build of the same ABI
     if not so:
         so = lib_path()
-        if _build.stale():
+        if _build.stale() and not os.environ.get("GT_NO_REBUILD"):   # GT_NO_REBUILD: use the built file as it is
             _build.build()
     L = C.CDLL(so)
     L.gt_strerror.restype = C.c_char_p

@@ -37,9 +37,10 @@ def test_demo_sort_bind_delete(gt, tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     lines = r.stdout.splitlines()
     sort = json.loads(lines[0].split("-> ", 1)[1])
-    # F1 (NV3 ring, PHB elsewhere): both nodes still have an NV3 pair free -> cost 3; the default cost table runs up
-    # to 15 (codes 12-15 are user defined), so the score is floor(10 * (15 - 3) / 15) = 8
-    assert sort == [{"Host": "node-a", "Score": 8}, {"Host": "node-b", "Score": 8}]
+    # F1 (NV3 ring, PHB elsewhere): both nodes still have an NV3 pair free -> cost 3; the score is normalised by the
+    # largest cost among the table's link kinds (SYS = 11 in the default table; user-defined codes 12-15 stay out),
+    # so it is floor(10 * (11 - 3) / 11) = 7
+    assert sort == [{"Host": "node-a", "Score": 7}, {"Host": "node-b", "Score": 7}]
     assert json.loads(lines[1].split("-> ", 1)[1]) == {"Error": ""}
     ann = dict(l.split(": ", 1) for l in lines[2:5])
     # node-b has GPUs 2,3 taken: the lowest-mask NV3 pair left is {0,1}
