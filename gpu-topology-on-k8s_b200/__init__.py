@@ -32,6 +32,8 @@ EXPORTS = [
     "gt_wire_parse_extender_args", "gt_wire_host_priorities", "gt_wire_parse_binding_args", "gt_wire_binding_result",
     "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
     "gt_level_from_p2plink", "gt_levels_from_p2plink", "gt_lut_cmax",
+    "gt_time_pass_rotated", "gt_best_node_local", "gt_comm_share",
+    "gt_host_free", "gt_host_free_changed", "gt_host_scores",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -161,6 +163,15 @@ def _lib():
     L.gt_count_subsets.argtypes = [C.c_void_p, u64p, u64p]
     L.gt_time_kernel.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_float)]
     L.gt_comm_unique_id.argtypes = [u8p]
+    if hasattr(L, "gt_host_free"):      # (an older build of the ABI loaded through GT_LIB for an A/B run may lack these)
+        L.gt_time_pass_rotated.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]
+        L.gt_best_node_local.argtypes = [C.c_void_p, u64p]
+        L.gt_comm_share.argtypes = [C.c_void_p, C.c_void_p]
+        L.gt_host_free.argtypes = [C.c_void_p]
+        L.gt_host_free.restype = C.POINTER(C.c_uint16)
+        L.gt_host_free_changed.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+        L.gt_host_scores.argtypes = [C.c_void_p]
+        L.gt_host_scores.restype = C.POINTER(C.c_uint8)
     L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
     L.gt_schedule.argtypes = [C.c_void_p, u8p, u32p, C.c_uint32, u32p, u16p, u64p]
@@ -352,6 +363,26 @@ class Allocator:
         """`sort` verb into a caller buffer (numpy u8[n_nodes], ideally pinned); place: optional u64[16]."""
         self._ck(self._L.gt_ext_sort(self._h, gpu_count, _p(scores, u8p), _p(place, u64p)), "gt_ext_sort")
 
+    def host_free(self):
+        """The context's pinned mirror of the free masks as a numpy view (max_nodes u16): edit in place, then
+        host_free_changed()."""
+        ptr = self._L.gt_host_free(self._h)
+        if not ptr:
+            raise GtError(-3, "gt_host_free", self._L.gt_last_error(self._h).decode())
+        return np.ctypeslib.as_array(ptr, shape=(self.max_nodes,))
+
+    def host_free_changed(self, first=0, count=None):
+        self._ck(self._L.gt_host_free_changed(self._h, first, self.num_nodes if count is None else count),
+                 "gt_host_free_changed")
+
+    def host_scores(self):
+        """The mapped pinned buffer the `sort` verb's scores land in (n_nodes u8), valid until the next ext_sort."""
+        return np.ctypeslib.as_array(self._L.gt_host_scores(self._h), shape=(self.num_nodes,))
+
+    def ext_sort_inplace(self, gpu_count, place=None):
+        """`sort` verb without the copy out: scores are read from host_scores()."""
+        self._ck(self._L.gt_ext_sort(self._h, gpu_count, None, _p(place, u64p)), "gt_ext_sort")
+
     def score_dirty(self):
         self._ck(self._L.gt_score_dirty(self._h), "gt_score_dirty")
 
@@ -406,9 +437,31 @@ class Allocator:
         self._ck(self._L.gt_time_kernel(self._h, which.encode(), iters, C.byref(ms)), "gt_time_kernel")
         return float(ms.value)
 
+    def comm_share(self, owner):
+        """Join the communicator of another Allocator of this process on the same device (it must be closed last)."""
+        self._ck(self._L.gt_comm_share(self._h, owner._h), "gt_comm_share")
+        self._comm_owner = owner      # keeps the lender alive
+
+    def best_node_local(self):
+        """This rank's own 16 placement keys (no exchange), recomputed from its best table."""
+        out = np.zeros(16, np.uint64)
+        self._ck(self._L.gt_best_node_local(self._h, _p(out, u64p)), "gt_best_node_local")
+        return out
+
     def comm_init(self, unique_id, rank, world):
         uid = np.ascontiguousarray(unique_id, np.uint8)
         self._ck(self._L.gt_comm_init(self._h, _p(uid, u8p), rank, world), "gt_comm_init")
+
+
+def time_pass_rotated(allocators, iters=64):
+    """(K0, K1, K0+K1) microseconds per launch, each kernel timed alone while the contexts take turns (cold L2 once
+    their tables exceed it)."""
+    arr = (C.c_void_p * len(allocators))(*[a._h.value for a in allocators])
+    out = (C.c_float * 3)()
+    rc = _lib().gt_time_pass_rotated(arr, len(allocators), iters, out)
+    if rc:
+        raise GtError(rc, "gt_time_pass_rotated", _lib().gt_last_error(allocators[0]._h).decode())
+    return tuple(float(x) for x in out)
 
 
 def place_fields(key):

@@ -101,10 +101,15 @@ struct gt_ctx {
     unsigned long long *peer_inbox[gt::kMaxPeers] = {};
     unsigned long long *d_xflags = nullptr;     // [0] K1's pass number, [1 + parity] number of the last finished exchange
     uint64_t k1_seq = 0, xchg_seq = 0, parity_seq[2] = {0, 0};
+    uint64_t *xchg_seq_p = nullptr;             // the exchange counter in use: the own one, or the lender's (gt_comm_share)
+    bool comm_borrowed = false;                 // communicator, communication stream and inboxes belong to another context
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
-    uint8_t *h_scores = nullptr;                // mapped pinned: k_sort_scores writes the reply straight to the host
+    uint8_t *d_scores = nullptr;                // one score byte per node, left by a pass that ran for a `sort` call
+    uint32_t want_score_m = 0;                  // request size the pass being enqueued shall leave scores for (0 = none)
+    uint32_t scores_m = 0;                      // request size d_scores is valid for (0 = stale)
+    uint8_t *h_scores = nullptr;                // mapped pinned: the score kernels write the reply straight to the host
     uint32_t *d_scores_map = nullptr;           // device view of h_scores
     unsigned long long *h_place_map = nullptr, *d_place_map = nullptr;   // same for the 16 placement keys
 #ifdef GT_TRACE
@@ -155,7 +160,7 @@ int fail(gt_ctx *c, int code, const char *fmt, const char *detail = "")
     do {                                                                          \
         cudaError_t e__ = (call);                                                 \
         if (e__ != cudaSuccess) {                                                 \
-            if (c) snprintf((c)->err, sizeof(c)->err, "%s: %s", #call, cudaGetErrorString(e__)); \
+            if (c) snprintf((c)->err, sizeof(c)->err, "%.160s: %s", #call, cudaGetErrorString(e__)); \
             return e__ == cudaErrorMemoryAllocation ? GT_ERR_NOMEM : GT_ERR_CUDA; \
         }                                                                         \
     } while (0)
@@ -248,6 +253,11 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
     p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
     p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
     p.seq_flag = nullptr; p.seq = 0;
+    p.scores = nullptr; p.score_k = 0; p.score_den = 0;
+    if (c->want_score_m && fold_into) {   // full pass on behalf of a `sort` call: one score byte per node on the way
+        const uint32_t m = c->want_score_m;
+        p.scores = c->d_scores; p.score_k = m; p.score_den = gt_lut_cmax(c->lut) * (m * (m - 1) / 2);
+    }
 #ifdef GT_TRACE
     p.trace = c->d_trace;
 #endif
@@ -271,8 +281,23 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus, (const uint16_t *)c->d_free, d_ids, n,
-                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place, wait_flag, wait_val));
+                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place, wait_flag, wait_val,
+                                  (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr)));
     c->launches++;
+    return GT_OK;
+}
+
+constexpr uint32_t kPipeMinNodes = 4096;
+
+// k_score_pipe needs more dynamic shared memory than the default limit: raised once per device
+int pipe_ready(gt_ctx *c)
+{
+    static std::mutex mu;
+    static bool done[64] = {};
+    std::lock_guard<std::mutex> lock(mu);
+    if (c->device >= 0 && c->device < 64 && done[c->device]) return GT_OK;
+    GT_CUDA(c, cudaFuncSetAttribute(gt::k_score_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(gt::pipe::Shared)));
+    if (c->device >= 0 && c->device < 64) done[c->device] = true;
     return GT_OK;
 }
 
@@ -296,7 +321,19 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
         prm.seq_flag = c->d_xflags;
         prm.seq = ++c->k1_seq;
     }
-
+    // full passes over enough nodes to give every SM several units: the producer / consumer form of K1 (one CTA per SM)
+    static const bool no_pipe = getenv("GT_NO_PIPE") != nullptr;   // profiling aid
+    if (fold && !no_pipe && n >= kPipeMinNodes) {
+        int rcp = pipe_ready(c);
+        if (rcp != GT_OK) return rcp;
+        cfg.gridDim = dim3(std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms));
+        cfg.blockDim = dim3(gt::pipe::kCta);
+        cfg.dynamicSmemBytes = sizeof(gt::pipe::Shared);
+        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score_pipe, prm));
+        c->launches++;
+        c->place_cur = fold;
+        return GT_OK;
+    }
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, prm));
     c->launches++;
     if (fold) c->place_cur = fold;
@@ -334,7 +371,8 @@ int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity, bool fla
         prm.k1_val = c->k1_seq;
         for (int q = 0; q < c->world; q++) prm.inbox[q] = c->peer_inbox[q];
         prm.done_flag = c->d_xflags + 1 + parity;
-        prm.seq = ++c->xchg_seq;
+        prm.err_flag = c->d_xflags + 3;
+        prm.seq = ++*c->xchg_seq_p;
         // inbox slots alternate with the exchange number, which every rank counts alike; the local key-buffer parity
         // may drift between ranks (a rank-local gt_time_kernel runs passes the others do not)
         prm.rank = (uint32_t)c->rank; prm.world = (uint32_t)c->world; prm.parity = (uint32_t)(prm.seq & 1u);
@@ -351,6 +389,14 @@ int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity, bool fla
     c->comm_used[parity] = true;
     c->comm_last = (int)parity;
     return GT_OK;
+}
+
+// an exchange kernel gave up waiting for a peer (kernels.cuh, kExchangeTimeoutNs): the placement keys of this context
+// are this rank's own, not the cluster's
+int exchange_failed(gt_ctx *c)
+{
+    return fail(c, GT_ERR_STATE, "the min-exchange of the placement keys timed out waiting for a peer: a rank is gone, or the "
+                                 "ranks issued the passes of their contexts in different orders%s");
 }
 
 // before a pass overwrites place[parity]: the exchange that last used that buffer must be finished.
@@ -373,10 +419,13 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
         cudaGraph_t graph = nullptr;
         const uint64_t before = c->launches;
         GT_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        const uint32_t want = c->want_score_m;
+        c->want_score_m = 0;            // the captured kernels are replayed for every later pass: no per-call parameters
         int rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, parity));
         if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, parity));
         if (rc == GT_OK) rc = launch_singular(c, nullptr, c->n_nodes, bin_place(c, parity));
         cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        c->want_score_m = want;
         c->launches = before;
         if (rc != GT_OK || e != cudaSuccess || !graph) {
             cudaGetLastError();
@@ -461,6 +510,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     // plain K0 -> K1 pass with peers: all cross-stream ordering through device flags (see exchange_min)
     bool flagged = c->comm && c->p2p && !d_ids && n && !memo_pass && !graph && c->k1_policy == GT_K1_FIRST_UNUSED;
     if ((rc = wait_place_free(c, par, flagged)) != GT_OK) return rc;
+    c->scores_m = 0;
     if (!d_ids && n) {
         bool done = false;
         if (memo_pass) {
@@ -480,6 +530,7 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
                                  c->parity_seq[par])) != GT_OK) return rc;
             if ((rc = launch_score(c, n, bin_place(c, par), false, flagged)) != GT_OK) return rc;
             if ((rc = launch_singular(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
+            c->scores_m = c->want_score_m;
         } else {
             flagged = false;
         }
@@ -534,6 +585,7 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
     gt_ctx *c = new (std::nothrow) gt_ctx();
     if (!c) return GT_ERR_NOMEM;
     c->err[0] = 0;
+    c->xchg_seq_p = &c->xchg_seq;
     c->device = cfg->device;
     c->cap = cfg->max_nodes;
     c->first_node = cfg->first_node;
@@ -571,9 +623,11 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_peak_out, 64));
         GT_CUDA(c, cudaMalloc(&c->d_xflags, 4 * sizeof(unsigned long long)));
         GT_CUDA(c, cudaMemset(c->d_xflags, 0, 4 * sizeof(unsigned long long)));
-        GT_CUDA(c, cudaHostAlloc(&c->h_scores, (N + 3) / 4 * 4, cudaHostAllocMapped));
+        GT_CUDA(c, cudaMalloc(&c->d_scores, (N + 15) / 16 * 16));
+        GT_CUDA(c, cudaHostAlloc(&c->h_scores, (N + 15) / 16 * 16, cudaHostAllocMapped));
         GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_scores_map, c->h_scores, 0));
-        GT_CUDA(c, cudaHostAlloc(&c->h_place_map, 16 * sizeof(unsigned long long), cudaHostAllocMapped));
+        GT_CUDA(c, cudaHostAlloc(&c->h_place_map, 17 * sizeof(unsigned long long), cudaHostAllocMapped));
+        c->h_place_map[16] = 0;
         GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_place_map, c->h_place_map, 0));
 #ifdef GT_TRACE
         GT_CUDA(c, cudaMalloc(&c->d_trace, (size_t)c->num_sms * 8 * 4 * gt::kTraceSlots * 8));
@@ -589,7 +643,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaHostAlloc(&c->h_ngpus, N, cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_ids, N * 4, cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_masks, N * 2, cudaHostAllocDefault));
-        GT_CUDA(c, cudaHostAlloc(&c->h_place, 16 * sizeof(unsigned long long), cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_place, 17 * sizeof(unsigned long long), cudaHostAllocDefault));
+        c->h_place[16] = 0;
         GT_CUDA(c, cudaHostAlloc(&c->h_row, 64, cudaHostAllocDefault));
         GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_h2d, cudaEventDisableTiming));
         memset(c->h_free, 0, N * 2);
@@ -612,7 +667,7 @@ void gt_destroy(gt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    if (c->comm) {
+    if (c->comm && !c->comm_borrowed) {
         NcclApi *api = nccl_api();
         if (api) api->CommDestroy(c->comm);
     }
@@ -620,9 +675,9 @@ void gt_destroy(gt_ctx *c)
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_memo); cudaFree(c->d_row0); cudaFree(c->d_node_class); cudaFree(c->d_place);
     cudaFree(c->d_tree); cudaFree(c->d_gaia_out);
     for (int q = 0; q < gt::kMaxPeers; q++)
-        if (c->peer_inbox[q] && c->peer_inbox[q] != c->d_inbox) cudaIpcCloseMemHandle(c->peer_inbox[q]);
+        if (!c->comm_borrowed && c->peer_inbox[q] && c->peer_inbox[q] != c->d_inbox) cudaIpcCloseMemHandle(c->peer_inbox[q]);
     cudaFree(c->d_inbox); cudaFree(c->d_xflags);
-    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
+    cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_scores); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
     cudaFreeHost(c->h_place); cudaFreeHost(c->h_row);
     for (auto &g : c->step_exec)
@@ -870,7 +925,10 @@ int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place
     }
     if (c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
     GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    if (c->comm && c->p2p)
+        GT_CUDA(c, cudaMemcpyAsync(c->h_place + 16, c->d_xflags + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->comm && c->p2p && c->h_place[16] != 0) return exchange_failed(c);
     for (uint32_t i = 0; i < nreq; i++)
         out_place[i] = (k[i] >= 1 && k[i] <= 16) ? (uint64_t)c->h_place[k[i] - 1] : GT_NO_PLACE;
     return GT_OK;
@@ -971,6 +1029,77 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     if ((rc = enqueue_scoring(c, nullptr, c->n_nodes)) != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
     *out_ms = ms / (float)iters;
+    return GT_OK;
+}
+
+// K0 and K1 timed one by one while the contexts take turns: with more replicas than fit the L2 every launch finds
+// its tables in DRAM, as the launches of a rotated scoring loop do.  Events sit between the kernels, so each runs
+// alone (no programmatic overlap with its neighbour): out_us = {K0, K1, K0 + K1} averages per launch.
+int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float out_us[3])
+{
+    if (!ctxs || !n_ctx || !iters || !out_us) return GT_ERR_INVALID;
+    gt_ctx *c0 = ctxs[0];
+    if (!c0) return GT_ERR_INVALID;
+    for (uint32_t i = 0; i < n_ctx; i++)
+        if (!ctxs[i] || ctxs[i]->device != c0->device || ctxs[i]->stream != c0->stream || !ctxs[i]->n_nodes)
+            return fail(c0, GT_ERR_INVALID, "gt_time_pass_rotated: contexts must share device and stream%s");
+    GT_CUDA(c0, cudaSetDevice(c0->device));
+    iters = std::min<uint32_t>(iters, 256);
+    std::vector<cudaEvent_t> ev((size_t)iters * 3);
+    for (auto &e : ev) GT_CUDA(c0, cudaEventCreate(&e));
+    int rc = GT_OK;
+    for (uint32_t i = 0; i < n_ctx && rc == GT_OK; i++) {
+        gt_ctx *c = ctxs[i];
+        if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+        rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
+        clear_dirty(c);
+    }
+    for (uint32_t it = 0; it < iters + n_ctx && rc == GT_OK; it++) {   // first round over the contexts: warm-up
+        gt_ctx *c = ctxs[it % n_ctx];
+        void *saved = c->comm;
+        c->comm = nullptr;   // a local measurement: other ranks are not in this call
+        const bool timed = it >= n_ctx;
+        cudaEvent_t *e = timed ? &ev[(size_t)(it - n_ctx) * 3] : nullptr;
+        if (timed) cudaEventRecord(e[0], c->stream);
+        rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
+        if (timed) cudaEventRecord(e[1], c->stream);
+        if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, 0));
+        if (timed) cudaEventRecord(e[2], c->stream);
+        c->comm = saved;
+        c->place_valid = false;
+    }
+    GT_CUDA(c0, cudaStreamSynchronize(c0->stream));
+    double sum[3] = {0, 0, 0};
+    for (uint32_t it = 0; it < iters && rc == GT_OK; it++) {
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, ev[(size_t)it * 3], ev[(size_t)it * 3 + 1]);
+        cudaEventElapsedTime(&b, ev[(size_t)it * 3 + 1], ev[(size_t)it * 3 + 2]);
+        sum[0] += a; sum[1] += b; sum[2] += a + b;
+    }
+    for (auto &e : ev) cudaEventDestroy(e);
+    for (int q = 0; q < 3; q++) out_us[q] = (float)(sum[q] * 1e3 / iters);
+    return rc;
+}
+
+// This rank's own 16 placement keys, recomputed from its best table (K2) without any exchange: what a checker
+// min-combines over ranks to verify the exchanged keys.
+int gt_best_node_local(gt_ctx *c, uint64_t out_place[16])
+{
+    if (!c || !out_place) return GT_ERR_INVALID;
+    GT_CUDA(c, cudaSetDevice(c->device));
+    if (!c->best_valid || !c->dirty.empty() || !c->free_uploaded) return fail(c, GT_ERR_STATE, "gt_best_node_local: score first%s");
+    unsigned long long *scratch = c->d_place + 16;     // [1]: not used by any pass
+    GT_CUDA(c, cudaMemsetAsync(scratch, 0xFF, 16 * sizeof(unsigned long long), c->stream));
+    const size_t quarters = (size_t)c->n_nodes * 4;
+    const uint32_t grid = (uint32_t)std::min<size_t>((quarters + gt::kCta * 8 - 1) / (gt::kCta * 8), (size_t)c->num_sms * 4);
+    if (c->n_nodes) {
+        gt::k_argmin<<<std::max(grid, 1u), gt::kCta, 0, c->stream>>>(c->d_best, c->n_nodes, c->first_node, scratch);
+        c->launches++;
+        GT_CUDA(c, cudaGetLastError());
+    }
+    GT_CUDA(c, cudaMemcpyAsync(c->h_place, scratch, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    memcpy(out_place, c->h_place, 16 * sizeof(uint64_t));
     return GT_OK;
 }
 
@@ -1110,24 +1239,45 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     return setup_peer_exchange(c);
 }
 
+// A second context of the same process and device joins the communicator of `owner` instead of setting up its own
+// (one NCCL communicator and one set of peer inboxes per process is enough: the exchanges of all sharing contexts run
+// one after the other on the device's communication stream and count one common exchange number).  Every rank must
+// share the same way and issue the passes of its contexts in the same order.  `owner` must outlive `c`.
+int gt_comm_share(gt_ctx *c, gt_ctx *owner)
+{
+    if (!c || !owner || c == owner) return GT_ERR_INVALID;
+    if (c->comm) return fail(c, GT_ERR_STATE, "gt_comm_share: the context already has a communicator%s");
+    if (!owner->comm) return fail(c, GT_ERR_STATE, "gt_comm_share: the lending context has no communicator%s");
+    if (owner->device != c->device) return fail(c, GT_ERR_INVALID, "gt_comm_share: contexts on different devices%s");
+    GT_CUDA(c, cudaSetDevice(c->device));
+    c->comm = owner->comm;
+    c->comm_borrowed = true;
+    c->rank = owner->rank;
+    c->world = owner->world;
+    c->comm_stream = owner->comm_stream;
+    c->own_comm_stream = false;
+    c->p2p = owner->p2p;
+    for (int q = 0; q < gt::kMaxPeers; q++) c->peer_inbox[q] = owner->peer_inbox[q];
+    c->xchg_seq_p = owner->xchg_seq_p;
+    GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_pass, cudaEventDisableTiming));
+    for (auto &ev : c->ev_comm) GT_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    c->place_valid = false;
+    return GT_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // gt_schedule: the sequential sort -> bind loop, one event at a time.
 namespace {
 
 constexpr size_t kMemoMaxBytes = (size_t)1 << 30;
 
-// GPU fills best rows for every free mask of every topology class (3^n subsets per class)
-int build_memo(gt_ctx *c)
+// GPU fills best rows for (topology class, free mask) pairs: rows [row_lo, row_hi) of the row space in which class k
+// owns rows off[k] .. off[k] + 2^n_k - 1 (row = off[k] + free mask).  K0 + K1 over a pseudo-cluster with one node per row.
+int memo_rows(gt_ctx *c, const std::vector<std::string> &classes, const std::vector<size_t> &off, size_t row_lo, size_t row_hi,
+              uint32_t *out_rows)
 {
-    const uint32_t ncls = (uint32_t)c->class_tile.size();
-    if (c->memo_classes == ncls && c->memo_lut_version == c->lut_version) return GT_OK;
-    size_t rows = 0;
-    c->memo_off.assign(ncls, 0);
-    for (uint32_t k = 0; k < ncls; k++) {
-        c->memo_off[k] = rows;
-        rows += (size_t)1 << (uint8_t)c->class_tile[k][256];
-    }
-    if (rows * 64 > kMemoMaxBytes || rows > 0x7FFFFFFFull) return GT_ERR_RANGE;
+    if (row_hi <= row_lo) return GT_OK;
+    const size_t rows = row_hi - row_lo;
     gt_config cfg = {};
     cfg.struct_size = sizeof cfg;
     cfg.device = c->device;
@@ -1143,34 +1293,47 @@ int build_memo(gt_ctx *c)
     std::vector<uint8_t> lv, ng;
     std::vector<uint16_t> fr;
     const size_t batch = (size_t)1 << 16;
-    for (uint32_t k = 0; k < ncls && rc == GT_OK; k++) {
-        const uint32_t n = (uint8_t)c->class_tile[k][256];
-        const size_t cnt = (size_t)1 << n;
-        for (size_t b0 = 0; b0 < cnt && rc == GT_OK; b0 += batch) {
-            const size_t bn = std::min(batch, cnt - b0);
+    for (uint32_t k = 0; k < classes.size() && rc == GT_OK; k++) {
+        const uint32_t n = (uint8_t)classes[k][256];
+        const size_t c_lo = std::max(off[k], row_lo), c_hi = std::min(off[k] + ((size_t)1 << n), row_hi);
+        for (size_t b0 = c_lo; b0 < c_hi && rc == GT_OK; b0 += batch) {
+            const size_t bn = std::min(batch, c_hi - b0);
             lv.resize(bn * 256); ng.assign(bn, (uint8_t)n); fr.resize(bn);
             for (size_t i = 0; i < bn; i++) {
-                memcpy(&lv[i * 256], c->class_tile[k].data(), 256);
-                fr[i] = (uint16_t)(b0 + i);
+                memcpy(&lv[i * 256], classes[k].data(), 256);
+                fr[i] = (uint16_t)(b0 + i - off[k]);
             }
             if (gaia) {
                 ac.resize(bn * 16); sb.resize(bn * 16);
                 for (size_t i = 0; i < bn; i++) {
-                    memcpy(&ac[i * 16], c->class_tile[k].data() + 257, 16);
-                    memcpy(&sb[i * 16], c->class_tile[k].data() + 273, 32);
+                    memcpy(&ac[i * 16], classes[k].data() + 257, 16);
+                    memcpy(&sb[i * 16], classes[k].data() + 273, 32);
                 }
             }
-            rc = gt_load_nodes(m, (uint32_t)(c->memo_off[k] + b0), (uint32_t)bn, lv.data(), ng.data(),
+            rc = gt_load_nodes(m, (uint32_t)(b0 - row_lo), (uint32_t)bn, lv.data(), ng.data(),
                                gaia ? ac.data() : nullptr, gaia ? sb.data() : nullptr, fr.data());
         }
     }
-    if (rc == GT_OK) {
-        c->memo.resize(rows * 16);
-        rc = gt_score_all(m, c->memo.data());
-    }
+    if (rc == GT_OK) rc = gt_score_all(m, out_rows);
     if (rc != GT_OK) fail(c, rc, "gt_schedule: memo build: %s", gt_last_error(m));
     c->launches += gt_launch_count(m);
     gt_destroy(m);
+    return rc;
+}
+
+int build_memo(gt_ctx *c)
+{
+    const uint32_t ncls = (uint32_t)c->class_tile.size();
+    if (c->memo_classes == ncls && c->memo_lut_version == c->lut_version) return GT_OK;
+    size_t rows = 0;
+    c->memo_off.assign(ncls, 0);
+    for (uint32_t k = 0; k < ncls; k++) {
+        c->memo_off[k] = rows;
+        rows += (size_t)1 << (uint8_t)c->class_tile[k][256];
+    }
+    if (rows * 64 > kMemoMaxBytes || rows > 0x7FFFFFFFull) return GT_ERR_RANGE;
+    c->memo.resize(rows * 16);
+    int rc = memo_rows(c, c->class_tile, c->memo_off, 0, rows, c->memo.data());
     if (rc != GT_OK) return rc;
     c->memo_classes = ncls;
     c->memo_lut_version = c->lut_version;
@@ -1213,12 +1376,158 @@ inline unsigned long long place_key(uint32_t b, uint32_t global_node)
 
 }  // namespace
 
+// ---- gt_schedule on a sharded cluster (one rank per GPU).  The commit loop is sequential by definition: every pod
+// sees the previous pod's effect on whichever shard it landed.  What shards is the GPU work -- the (class, free mask)
+// table is built in `world` slices, one per GPU, and gathered -- while the host loop itself runs replicated: every
+// rank gathers the cluster's node states once (class, GPU count, free mask: 8 bytes per node), replays the same
+// events over the whole cluster with the same table, arrives at the same placements, and applies the ones that hit
+// its own shard to its tables.  No per-event exchange; outputs are identical on every rank.
+namespace {
+
+// all-gather of `bytes` per rank through the communicator (NCCL, staged through a scratch device buffer)
+int allgather_host(gt_ctx *c, const void *mine, size_t bytes, std::vector<uint8_t> &all)
+{
+    NcclApi *api = nccl_api();
+    if (!api || !api->AllGather) return fail(c, GT_ERR_NCCL, "gt_schedule: ncclAllGather unavailable%s");
+    struct Buf { uint8_t *p = nullptr; ~Buf() { cudaFree(p); } } d;
+    const size_t w = (size_t)c->world;
+    GT_CUDA(c, cudaMalloc(&d.p, bytes * (w + 1)));
+    GT_CUDA(c, cudaMemcpy(d.p + bytes * w, mine, bytes, cudaMemcpyHostToDevice));
+    int e = api->AllGather(d.p + bytes * w, d.p, bytes, kNcclUint8, c->comm, c->comm_stream);
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllGather: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
+    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    all.resize(bytes * w);
+    GT_CUDA(c, cudaMemcpy(all.data(), d.p, bytes * w, cudaMemcpyDeviceToHost));
+    return GT_OK;
+}
+
+struct NodeState { uint32_t cls; uint16_t free; uint8_t ngpus, pad; };
+
+int schedule_sharded(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
+                     uint16_t *out_mask, uint64_t *out_placed)
+{
+    if (c->flags & GT_FLAG_NO_MEMO) return fail(c, GT_ERR_STATE, "gt_schedule: GT_FLAG_NO_MEMO is not available on a sharded context%s");
+    GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    int rc;
+    if ((rc = mirror_writable(c)) != GT_OK) return rc;
+    const uint32_t W = (uint32_t)c->world;
+    std::vector<uint8_t> all;
+    // shard sizes, first nodes, class counts
+    const uint32_t hdr[4] = {c->n_nodes, c->first_node, (uint32_t)c->class_tile.size(), 0};
+    if ((rc = allgather_host(c, hdr, sizeof hdr, all)) != GT_OK) return rc;
+    std::vector<uint32_t> n_of(W), first_of(W), ncls_of(W), base_of(W);
+    uint32_t max_n = 1, max_cls = 1, N = 0;
+    for (uint32_t r = 0; r < W; r++) {
+        const uint32_t *h = reinterpret_cast<const uint32_t *>(all.data()) + 4 * r;
+        n_of[r] = h[0]; first_of[r] = h[1]; ncls_of[r] = h[2];
+        base_of[r] = N; N += h[0];
+        max_n = std::max(max_n, h[0]); max_cls = std::max(max_cls, h[2]);
+    }
+    // one class list for the whole cluster: every rank's classes in rank order, duplicates folded
+    const size_t key_len = c->k1_policy == GT_K1_GAIA_SINGULAR ? 257 + 16 + 32 : 257;
+    std::vector<uint8_t> mine((size_t)max_cls * key_len, 0);
+    for (size_t k = 0; k < c->class_tile.size(); k++) memcpy(&mine[k * key_len], c->class_tile[k].data(), key_len);
+    if ((rc = allgather_host(c, mine.data(), mine.size(), all)) != GT_OK) return rc;
+    std::unordered_map<std::string, uint32_t> gid_of;
+    std::vector<std::string> gclass;
+    std::vector<uint32_t> my_map(c->class_tile.size());
+    for (uint32_t r = 0; r < W; r++)
+        for (uint32_t k = 0; k < ncls_of[r]; k++) {
+            std::string key(reinterpret_cast<const char *>(&all[((size_t)r * max_cls + k) * key_len]), key_len);
+            auto it = gid_of.find(key);
+            if (it == gid_of.end()) {
+                it = gid_of.emplace(key, (uint32_t)gclass.size()).first;
+                gclass.push_back(key);
+            }
+            if (r == (uint32_t)c->rank) my_map[k] = it->second;
+        }
+    // the table: this rank scores its slice of the rows, everybody gets all of them
+    std::vector<size_t> off(gclass.size());
+    size_t rows = 0;
+    for (size_t k = 0; k < gclass.size(); k++) { off[k] = rows; rows += (size_t)1 << (uint8_t)gclass[k][256]; }
+    if (rows * 64 > kMemoMaxBytes) return fail(c, GT_ERR_RANGE, "gt_schedule: too many distinct topologies for the table%s");
+    const size_t per = (rows + W - 1) / W, lo = std::min(rows, per * (size_t)c->rank), hi = std::min(rows, lo + per);
+    std::vector<uint32_t> slice(per * 16, GT_INFEASIBLE);
+    if ((rc = memo_rows(c, gclass, off, lo, hi, slice.data())) != GT_OK) return rc;
+    if ((rc = allgather_host(c, slice.data(), per * 64, all)) != GT_OK) return rc;
+    std::vector<uint32_t> memo(rows * 16);
+    memcpy(memo.data(), all.data(), rows * 64);       // slices are contiguous in rank order; the tail of the last is padding
+    // node states
+    std::vector<NodeState> st(max_n);
+    for (uint32_t i = 0; i < c->n_nodes; i++) st[i] = NodeState{my_map[c->node_class[i]], c->h_free[i], c->h_ngpus[i], 0};
+    if ((rc = allgather_host(c, st.data(), (size_t)max_n * sizeof(NodeState), all)) != GT_OK) return rc;
+    std::vector<NodeState> node(N);
+    std::vector<uint32_t> gnode(N);
+    for (uint32_t r = 0; r < W; r++)
+        for (uint32_t i = 0; i < n_of[r]; i++) {
+            node[base_of[r] + i] = reinterpret_cast<const NodeState *>(all.data())[(size_t)r * max_n + i];
+            gnode[base_of[r] + i] = first_of[r] + i;
+        }
+    auto pos_of = [&](uint32_t g) -> uint32_t {
+        for (uint32_t r = 0; r < W; r++)
+            if (g >= first_of[r] && g - first_of[r] < n_of[r]) return base_of[r] + (g - first_of[r]);
+        return 0xFFFFFFFFu;
+    };
+    const uint32_t my_lo = base_of[c->rank], my_hi = my_lo + c->n_nodes;
+    // the replicated loop
+    MinTree tree;
+    tree.init(std::max(N, 1u));
+    auto row_of = [&](uint32_t pos) -> const uint32_t * {
+        const NodeState &s2 = node[pos];
+        return &memo[(off[s2.cls] + (s2.free & ((1u << s2.ngpus) - 1u))) * 16];
+    };
+    for (uint32_t pos = 0; pos < N; pos++) {
+        const uint32_t *row = row_of(pos);
+        for (int k = 0; k < 16; k++) tree.t[k][tree.leaves + pos] = place_key(row[k], gnode[pos]);
+    }
+    tree.build();
+    auto refresh = [&](uint32_t pos) {
+        const uint32_t *row = row_of(pos);
+        for (int k = 0; k < 16; k++) tree.set(k, pos, place_key(row[k], gnode[pos]));
+        if (pos >= my_lo && pos < my_hi) {           // lands on this rank's shard: its tables follow
+            c->h_free[pos - my_lo] = node[pos].free;
+            mark_dirty(c, pos - my_lo);
+        }
+    };
+    uint64_t placed = 0;
+    std::vector<uint32_t> live_pos;
+    std::vector<uint16_t> live_mask;
+    for (uint32_t e = 0; e < n_events; e++) {
+        out_node[e] = 0xFFFFFFFFu; out_mask[e] = 0;
+        if (ev_k[e] == 0) {
+            if (live_pos.empty()) continue;
+            const size_t idx = ev_arg[e] % live_pos.size();
+            const uint32_t pos = live_pos[idx]; const uint16_t m = live_mask[idx];
+            node[pos].free |= m;
+            out_node[e] = gnode[pos]; out_mask[e] = m;
+            live_pos[idx] = live_pos.back(); live_pos.pop_back();
+            live_mask[idx] = live_mask.back(); live_mask.pop_back();
+            refresh(pos);
+        } else if (ev_k[e] <= 16) {
+            const unsigned long long key = tree.t[ev_k[e] - 1][1];
+            if (key == ~0ull) continue;
+            const uint32_t pos = pos_of(GT_PLACE_NODE(key)); const uint16_t m = (uint16_t)GT_PLACE_MASK(key);
+            if (pos == 0xFFFFFFFFu) return fail(c, GT_ERR_STATE, "gt_schedule: overlapping or inconsistent shard ranges%s");
+            node[pos].free &= (uint16_t)~m;
+            out_node[e] = gnode[pos]; out_mask[e] = m;
+            live_pos.push_back(pos); live_mask.push_back(m);
+            placed++;
+            refresh(pos);
+        }
+    }
+    if (out_placed) *out_placed = placed;
+    return GT_OK;
+}
+
+}  // namespace
+
 int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
                 uint16_t *out_mask, uint64_t *out_placed)
 {
     if (!c || (n_events && (!ev_k || !ev_arg || !out_node || !out_mask))) return GT_ERR_INVALID;
-    if (c->comm) return fail(c, GT_ERR_STATE, "gt_schedule: not available on a sharded (multi-rank) context%s");
     GT_CUDA(c, cudaSetDevice(c->device));
+    if (c->comm) return schedule_sharded(c, ev_k, ev_arg, n_events, out_node, out_mask, out_placed);
     uint64_t placed = 0;
     std::vector<uint32_t> live_node;
     std::vector<uint16_t> live_mask;
@@ -1303,26 +1612,66 @@ int gt_schedule(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t
 // "sort" verb (design.md:99,118): one score 0..10 per node for a pod asking for m GPUs
 int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
 {
-    if (!c || !out_scores || m < 1 || m > 16) return GT_ERR_INVALID;
+    if (!c || m < 1 || m > 16) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
     int rc = GT_OK;
-    if (!c->best_valid || !c->free_uploaded) rc = gt_score_all_async(c);
-    else if (!c->dirty.empty()) rc = gt_score_dirty(c);
+    if (!c->best_valid || !c->free_uploaded) {
+        c->want_score_m = m;             // the pass leaves one score byte per node for this request size as it goes
+        rc = gt_score_all_async(c);
+        c->want_score_m = 0;
+    } else if (!c->dirty.empty()) {
+        rc = gt_score_dirty(c);
+    }
     if (rc != GT_OK) return rc;
     if (!c->n_nodes) return GT_OK;
     const uint32_t cmax = gt_lut_cmax(c->lut);
     if (out_place && c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
-    // the kernel stores scores and keys into mapped pinned memory: no device-to-host copy behind it
-    const uint32_t threads = (c->n_nodes + 3) / 4;
-    gt::k_sort_scores<<<(std::max(threads, 16u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-        c->d_best, c->n_nodes, m, cmax, c->d_scores_map, c->place_cur, out_place ? c->d_place_map : nullptr);
+    // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them
+    if (c->scores_m == m) {
+        const uint32_t threads = (c->n_nodes + 15) / 16;
+        gt::k_scores_out<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+            c->d_scores, c->d_best, c->n_nodes, m, cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map),
+            c->place_cur, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+    } else {
+        const uint32_t threads = (c->n_nodes + 3) / 4;
+        gt::k_sort_scores<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
+            c->d_best, c->n_nodes, m, cmax, c->d_scores_map, c->place_cur, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+    }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
-    memcpy(out_scores, c->h_scores, c->n_nodes);
-    if (out_place) memcpy(out_place, c->h_place_map, 16 * sizeof(uint64_t));
+    if (out_scores) memcpy(out_scores, c->h_scores, c->n_nodes);   // NULL: the caller reads gt_host_scores() in place
+    if (out_place) {
+        if (c->comm && c->p2p && c->h_place_map[16] != 0) return exchange_failed(c);
+        memcpy(out_place, c->h_place_map, 16 * sizeof(uint64_t));
+    }
     return GT_OK;
 }
+
+// Zero-copy surface for callers that keep their cluster state in pinned memory: the context's own pinned mirror of the
+// free masks (edit in place, then say what changed) and the mapped buffer the `sort` verb's scores land in.
+uint16_t *gt_host_free(gt_ctx *c)
+{
+    if (!c) return nullptr;
+    if (mirror_writable(c) != GT_OK) return nullptr;   // an upload that still reads the mirror has to finish first
+    return c->h_free;
+}
+
+int gt_host_free_changed(gt_ctx *c, uint32_t first, uint32_t count)
+{
+    if (!c) return GT_ERR_INVALID;
+    if ((uint64_t)first + count > c->n_nodes) return fail(c, GT_ERR_RANGE, "gt_host_free_changed: range exceeds loaded nodes%s");
+    if (first == 0 && count == c->n_nodes) {       // whole shard: one bulk copy, every node rescored by the next pass
+        c->free_uploaded = false;
+        clear_dirty(c);
+        c->best_valid = c->place_valid = false;
+        return GT_OK;
+    }
+    for (uint32_t i = 0; i < count; i++) mark_dirty(c, first + i);
+    return GT_OK;
+}
+
+const uint8_t *gt_host_scores(gt_ctx *c) { return c ? c->h_scores : nullptr; }
 
 // "bind" verb (design.md:100,119,223-234): GPUs for the pod on the chosen node, commit, pod annotations
 int gt_ext_bind(gt_ctx *c, uint32_t node, uint32_t m, int64_t assume_time, uint16_t *out_mask, char *out_annotations,
@@ -1564,11 +1913,12 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr, nullptr, 0ull);
+                                                                     nullptr, nullptr, 0ull, nullptr);
     gt::ScoreParams prm;
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;
     prm.seq_flag = nullptr; prm.seq = 0;
+    prm.scores = nullptr; prm.score_k = 0; prm.score_den = 0;
     const uint32_t grid = std::min<uint32_t>(n_nodes / 8 + gt::kBins, (uint32_t)sms * gt::kScoreMinCtas);
     gt::k_score<<<grid, gt::kScoreCta, 0, s>>>(prm);
     e = cudaGetLastError();

@@ -38,7 +38,10 @@ constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
 constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the register budget is set for
 constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
 constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 16: shifts banks between tiles)
-constexpr int kStageBytes = kTilesPerWarp * kTileStride;   // staging buffer of a warp: 16 full tiles
+#ifndef GT_SMALL_SMEM
+#define GT_SMALL_SMEM 1   // one-lane-per-node units read their pair costs from tiles the warp staged in shared memory
+#endif
+constexpr int kStageBytes = (GT_SMALL_SMEM ? 32 : kTilesPerWarp) * kTileStride;   // staging buffer of a warp: 16 full tiles (32 for small units)
 constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
 
 struct ScoreParams {
@@ -54,6 +57,8 @@ struct ScoreParams {
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
     unsigned long long *seq_flag;   // multi-GPU: the last CTA publishes `seq` here once every fold into `place` is done
     unsigned long long seq;         // (k_exchange on the communication stream waits for it; null = nobody waits)
+    uint8_t *scores;                // `sort` verb inside the pass: HostPriority score 0..10 of every node for request size
+    uint32_t score_k, score_den;    // score_k (1..16; 0 = off), den = cmax * C(score_k, 2); see score_byte()
 #ifdef GT_TRACE
     unsigned long long *trace;   // [warps][kTraceSlots] (globaltimer ns << 8 | event id), debug builds only
 #endif
@@ -103,6 +108,17 @@ __device__ __forceinline__ int bin_order(int i)
     return (int)(((i < 12) ? (lo >> (5 * i)) : (hi >> (5 * (i - 12)))) & 31ull);
 }
 
+// HostPriority score of a best-table entry (design.md:205-217): floor(10 * (den - cost) / den), den = cmax * C(m,2);
+// a single GPU (den = 0) scores 10, an infeasible node 0.  kScorePending marks nodes whose rows several work units
+// build together (p >= 14): k_scores_out computes their score once the pass is over.
+constexpr uint32_t kScorePending = 0xFFu;
+__device__ __forceinline__ uint32_t score_byte(uint32_t b, uint32_t den)
+{
+    if (b == kInf) return 0u;
+    const uint32_t cost = b >> 16;
+    return den == 0u ? 10u : (cost >= den ? 0u : (10u * (den - cost)) / den);
+}
+
 // ---------------------------------------------------------------- load time
 // cost[i][j] = cost[j][i] = lut[levels[min(i,j)][max(i,j)]], cost[i][i] = 0: the upper triangle of the level
 // matrix is the one that counts (gputopo.h), and the scoring kernels rely on symmetric tiles with a
@@ -138,7 +154,8 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
                                               unsigned long long *__restrict__ place,
-                                              const unsigned long long *wait_flag, unsigned long long wait_val)
+                                              const unsigned long long *wait_flag, unsigned long long wait_val,
+                                              uint8_t *__restrict__ scores)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
@@ -155,6 +172,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     if (place && blockIdx.x == 0 && tid < 16) {
         // multi-GPU: the exchange that last used this key buffer (two passes ago) must have finished with it
         if (wait_flag) {
+            // (the exchange kernel sets its flag even when it gave up on a peer, so this ends within its time limit)
             while (*reinterpret_cast<const volatile unsigned long long *>(wait_flag) < wait_val) __nanosleep(64);
             __threadfence();   // acquire side of the exchange kernel's release (fence + flag store)
         }
@@ -175,6 +193,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
             uint4 *o = reinterpret_cast<uint4 *>(best + (size_t)node * 16);
             const uint4 inf = make_uint4(kInf, kInf, kInf, kInf);
             o[0] = inf; o[1] = inf; o[2] = inf; o[3] = inf;
+            if (scores) scores[node] = (uint8_t)kScorePending;
         }
     }
     __syncthreads();
@@ -278,6 +297,16 @@ __device__ __forceinline__ void score_small_any(int p, const uint8_t *tile, uint
     case 8: score_small<8, SMEM>(tile, f, out); break;
     default: break;
     }
+}
+
+// entry k-1 of a row held in registers (one-lane-per-node units have at most 8 feasible sizes)
+__device__ __forceinline__ uint32_t pick_row(const uint32_t (&out)[16], uint32_t k)
+{
+    uint32_t v = kInf;
+#pragma unroll
+    for (int q = 0; q < 8; q++)
+        if (k == (uint32_t)(q + 1)) v = out[q];
+    return v;
 }
 
 // The cluster argmin is carried in registers: lane k (< 16) of every warp holds the warp's best
@@ -433,6 +462,7 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
             const uint32_t nd = __ldg(list + first + s2);
             const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
             prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+            if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
             hb2.take(v, nd);
         }
         __syncwarp();
@@ -486,6 +516,9 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             if (p >= kSplitP) units = cnt << (p - 13);
             else if (p > 8) units = (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
             else units = (cnt + 31u) >> 5;
+#ifdef GT_BINMASK   // profiling builds only: score just the bins in the mask (results are incomplete)
+            if (!((GT_BINMASK >> p) & 1u)) units = 0;
+#endif
         }
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -535,14 +568,38 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 node = __ldg(prm.bin_list + at);
                 f = __ldg(prm.bin_free + at);
             }
+#if GT_SMALL_SMEM
+            // The unit's tiles travel as whole 16-byte rows, two nodes per load instruction (a half-warp per node,
+            // one lane per row), and only the rows of free GPUs: a handful of wide loads that touch one or two lines
+            // per node, instead of up to 28 byte loads per lane that touch 32 lines each -- those kept the SM's
+            // load pipe busy for a microsecond per unit.  Lanes then pick their pair costs out of shared memory.
+            {
+                const uint32_t row = lane & 15u;
+                __syncwarp();
+#pragma unroll 8
+                for (int t = 0; t < 16; t++) {
+                    const int s2 = 2 * t + (int)(lane >> 4);
+                    const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, s2);
+                    const uint32_t ff = __shfl_sync(0xFFFFFFFFu, f, s2);     // 0 for slots beyond the bin's end
+                    if ((ff >> row) & 1u)
+                        *reinterpret_cast<uint4 *>(ws.raw + s2 * kTileStride + row * 16) =
+                            __ldg(reinterpret_cast<const uint4 *>(prm.cost + (size_t)nd * 256) + row);
+                }
+                __syncwarp();
+            }
+            if (ok) {
+                score_small_any<true>(p, ws.raw + lane * kTileStride, f, out);
+#else
             if (ok) {
                 score_small_any<false>(p, prm.cost + (size_t)node * 256, f, out);
+#endif
                 GT_TR(20);   // small: gathers + tree done
                 uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)node * 16);
                 o[0] = make_uint4(out[0], out[1], out[2], out[3]);
                 o[1] = make_uint4(out[4], out[5], out[6], out[7]);
                 o[2] = make_uint4(kInf, kInf, kInf, kInf);
                 o[3] = make_uint4(kInf, kInf, kInf, kInf);
+                if (prm.score_k) prm.scores[node] = (uint8_t)score_byte(pick_row(out, prm.score_k), prm.score_den);
             }
             if (prm.fold_place) {
                 fold_small_warp4<0>(wb, out, node, lane);
@@ -590,6 +647,317 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     }
 }
 
+// ---------------------------------------------------------------- K1 as a producer / consumer pipeline (full passes)
+// Same enumeration, same units, same results as k_score; what changes is who waits for memory.  In k_score every warp
+// walks the chain ticket -> bin-list entry -> cost tiles (DRAM) -> set-up -> tree -> write-out by itself, twice per
+// pass on average, and the SM's issue slots stand idle through the first three links.  Here one CTA of 20 warps per SM
+// splits the roles: warp 0 (the producer) walks this SM's share of the units ahead of everybody else, reads their
+// bin-list entries and has the copy engine move each node's tile rows into a ring of shared-memory slots
+// (cp.async.bulk from this GPU's own cost table, one copy per node, completion counted by the slot's mbarrier); the
+// other 19 warps (consumers) take filled slots in order, run the unit out of shared memory, write its rows and hand the
+// slot back.  Units are dealt round-robin over the SMs in cost order (unit u belongs to CTA u mod gridDim.x): every SM
+// gets the same number of every unit type +-1, no ticket atomics.  Slot = 4608 bytes of tile rows (16 full tiles of a
+// many-lanes-per-node unit, or 32 nodes' rows 0..highest free GPU of a one-lane-per-node unit, 16 bytes of padding
+// between nodes against bank conflicts; a unit whose rows do not fit travels as two half units) + the unit's descriptor.
+namespace pipe {
+constexpr int kWarps = 20;                 // 1 producer + 19 consumers: what 96 registers per thread leave room for
+constexpr int kCta = kWarps * 32;
+constexpr int kSlots = 32;
+constexpr int kSlotRaw = 4608;
+constexpr uint32_t kPoison = 0xFFFFFFFFu;  // descriptor of the slots that tell the consumers to stop
+constexpr int kBatch = 8;                  // units whose bin-list entries the producer has in flight together
+
+struct Slot {
+    __align__(128) uint8_t raw[kSlotRaw];
+    uint32_t node[32];     // per slot lane: node (local index), 0xFFFFFFFF = none
+    uint32_t f[32];        // its free mask
+    uint16_t off[32];      // where its rows start in raw
+    uint32_t p, lu, live, pad;
+};
+struct Shared {
+    Slot slot[kSlots];
+    uint32_t best[kWarps][kTilesPerWarp][kBins];   // per consumer warp: per-k minima of the unit's nodes
+    unsigned long long full[kSlots], empty[kSlots];
+    unsigned long long place[16];
+    uint32_t cnt[kBins], end[kBins];
+    uint32_t next, n_units;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect(unsigned long long *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(unsigned long long *bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// a wait that cannot hang the GPU: a pipeline bug ends the kernel with an error after a second instead
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
+{
+    if (mbar_try(bar, parity)) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (uint32_t spins = 0;; spins++) {
+        if (mbar_try(bar, parity)) return;
+        if ((spins & 1023u) == 1023u) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > 1000000000ull) __trap();
+        }
+    }
+}
+// plain (non-multicast) bulk copy, global memory of this GPU -> this CTA's shared memory
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// where unit u of the pass lives: bin (hand-out order index i, advanced from the previous unit), its nodes
+struct UnitAt { uint32_t p, lu, first, live; };
+__device__ __forceinline__ UnitAt locate(const Shared &sh, uint32_t u, int &i)
+{
+    while (u >= sh.end[i]) i++;
+    UnitAt a;
+    a.p = (uint32_t)bin_order(i);
+    a.lu = u - (i ? sh.end[i - 1] : 0u);
+    const uint32_t cnt = sh.cnt[a.p];
+    if (a.p > 8) {
+        const uint32_t hb = a.p - 8;
+        if (hb <= 5) {
+            const uint32_t slots = 32u >> hb;
+            a.first = a.lu * slots;
+            a.live = min(slots, cnt - a.first);
+        } else {
+            a.first = a.lu >> (hb - 5);
+            a.live = 1;
+        }
+    } else {
+        a.first = a.lu * 32u;
+        a.live = min(32u, cnt - a.first);
+    }
+    return a;
+}
+}  // namespace pipe
+
+__global__ void __launch_bounds__(pipe::kCta, 1) k_score_pipe(ScoreParams prm)
+{
+    using namespace pipe;
+    extern __shared__ __align__(128) uint8_t pipe_smem[];
+    Shared &sh = *reinterpret_cast<Shared *>(pipe_smem);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid == 0) {
+        for (int q = 0; q < kSlots; q++) { mbar_init(&sh.full[q], 1); mbar_init(&sh.empty[q], 1); }
+        sh.next = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (tid < 16) sh.place[tid] = ~0ull;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible
+    if (warp == 0) {
+        uint32_t units = 0, cnt = 0;
+        int p = 0;
+        if (lane < (uint32_t)kBins) {
+            p = bin_order((int)lane);
+            cnt = prm.ctl[p];
+            sh.cnt[p] = cnt;
+            if (p >= kSplitP) units = cnt << (p - 13);
+            else if (p > 8) units = (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
+            else units = (cnt + 31u) >> 5;
+#ifdef GT_BINMASK   // profiling builds only: score just the bins in the mask (results are incomplete)
+            if (!((GT_BINMASK >> p) & 1u)) units = 0;
+#endif
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, units, d);
+            if (lane >= (uint32_t)d) units += o;
+        }
+        if (lane < (uint32_t)kBins) sh.end[lane] = units;
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, units, kBins - 1);
+        if (lane == 0) sh.n_units = total > blockIdx.x ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+    }
+    __syncthreads();
+    WarpBest wb;
+    wb.v = kInf; wb.node = 0xFFFFFFFFu;
+
+    if (warp == 0) {
+        // ------------------------------------------------ producer
+        const uint32_t n_units = sh.n_units, G = gridDim.x;
+        uint32_t q = 0;                 // slots filled so far (a unit takes one slot, sometimes two)
+        int i_load = 0, i_use = 0;
+        auto fill = [&](uint32_t p, uint32_t lu, uint32_t live, uint32_t node, uint32_t f, uint32_t bytes, uint32_t off) {
+            const uint32_t s = q % kSlots;
+            if (q >= (uint32_t)kSlots) mbar_wait(&sh.empty[s], ((q / kSlots) - 1u) & 1u);
+            Slot &sl = sh.slot[s];
+            sl.node[lane] = node; sl.f[lane] = f; sl.off[lane] = (uint16_t)off;
+            if (lane == 0) { sl.p = p; sl.lu = lu; sl.live = live; }
+            const uint32_t total = __reduce_add_sync(0xFFFFFFFFu, bytes);
+            __syncwarp();
+            if (lane == 0) mbar_arrive_expect(&sh.full[s], total);
+            __syncwarp();
+            if (bytes) bulk_g2s(sl.raw + off, prm.cost + (size_t)node * 256, bytes, &sh.full[s]);
+            q++;
+        };
+        for (uint32_t j0 = 0; j0 < n_units; j0 += kBatch) {
+            uint32_t nd[kBatch], fr[kBatch];
+#pragma unroll
+            for (int b = 0; b < kBatch; b++) {       // the batch's bin-list entries: one round trip for all of them
+                nd[b] = 0xFFFFFFFFu; fr[b] = 0;
+                if (j0 + b < n_units) {
+                    const UnitAt a = locate(sh, blockIdx.x + (j0 + b) * G, i_load);
+                    if (lane < a.live) {
+                        const size_t at = (size_t)a.p * prm.cap + a.first + lane;
+                        nd[b] = __ldg(prm.bin_list + at);
+                        fr[b] = __ldg(prm.bin_free + at);
+                    }
+                }
+            }
+#pragma unroll
+            for (int b = 0; b < kBatch; b++) {
+                if (j0 + b >= n_units) break;
+                const UnitAt a = locate(sh, blockIdx.x + (j0 + b) * G, i_use);
+                const uint32_t node = nd[b], f = fr[b];
+                if (a.p > 8) {           // whole tiles, 272 bytes apart
+                    fill(a.p, a.lu, a.live, node, f, lane < a.live ? 256u : 0u, lane * (uint32_t)kTileStride);
+                } else {                 // rows 0 .. highest free GPU, 16 bytes of padding behind every node
+                    const uint32_t bytes = f ? 16u * (32u - (uint32_t)__clz(f)) : 0u;
+                    uint32_t incl = bytes + 16u;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                        if (lane >= (uint32_t)d) incl += o;
+                    }
+                    const uint32_t all = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                    if (all <= (uint32_t)kSlotRaw) {
+                        fill(a.p, a.lu, a.live, node, f, bytes, incl - bytes - 16u);
+                    } else {             // many 16-GPU nodes among them: two half units
+                        const uint32_t half0 = __shfl_sync(0xFFFFFFFFu, incl, 15);
+                        const uint32_t n2 = __shfl_down_sync(0xFFFFFFFFu, node, 16), f2 = __shfl_down_sync(0xFFFFFFFFu, f, 16);
+                        const uint32_t b2 = __shfl_down_sync(0xFFFFFFFFu, bytes, 16), i2 = __shfl_down_sync(0xFFFFFFFFu, incl, 16);
+                        const bool lo = lane < 16;
+                        fill(a.p, a.lu, min(a.live, 16u), lo ? node : 0xFFFFFFFFu, lo ? f : 0u, lo ? bytes : 0u,
+                             lo ? incl - bytes - 16u : 0u);
+                        fill(a.p, a.lu, a.live > 16u ? a.live - 16u : 0u, lo ? n2 : 0xFFFFFFFFu, lo ? f2 : 0u, lo ? b2 : 0u,
+                             lo ? i2 - b2 - 16u - half0 : 0u);
+                    }
+                }
+            }
+        }
+        for (int w = 1; w < kWarps; w++) fill(kPoison, 0, 0, 0xFFFFFFFFu, 0, 0, 0);   // one stop sign per consumer
+    } else {
+        // ------------------------------------------------ consumers
+        uint32_t (*my_best)[kBins] = sh.best[warp];
+        for (;;) {
+            uint32_t q = 0;
+            if (lane == 0) q = atomicAdd(&sh.next, 1u);
+            q = __shfl_sync(0xFFFFFFFFu, q, 0);
+            const uint32_t s = q % kSlots;
+            mbar_wait(&sh.full[s], (q / kSlots) & 1u);
+            Slot &sl = sh.slot[s];
+            const uint32_t p = sl.p;
+            if (p == kPoison) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sh.empty[s]);
+                break;
+            }
+            const uint32_t live = sl.live;
+            if (p > 8) {
+                const int hb = (int)p - 8;
+                uint32_t slot, h;
+                if (hb <= 5) { slot = lane >> hb; h = lane & ((1u << hb) - 1u); }
+                else { slot = 0; h = ((sl.lu & ((1u << (hb - 5)) - 1u)) << 5) | lane; }
+                const bool active = slot < live;
+                for (uint32_t s2 = 0; s2 < live; s2++)
+                    if (lane < (uint32_t)kBins) my_best[s2][lane] = kInf;
+                __syncwarp();
+                if (active) score_big_lane(sl.raw + slot * kTileStride, sl.f[slot], hb, h, &my_best[slot][0]);
+                __syncwarp();
+                if (hb <= 5) {
+                    WarpBest hb2;
+                    hb2.v = kInf; hb2.node = 0xFFFFFFFFu;
+                    for (uint32_t s2 = lane >> 4; s2 < live; s2 += 2) {
+                        const uint32_t nd = sl.node[s2];
+                        const uint32_t v = my_best[s2][(lane & 15u) + 1u];
+                        prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+                        if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
+                        hb2.take(v, nd);
+                    }
+                    __syncwarp();
+                    const uint32_t ov = __shfl_xor_sync(0xFFFFFFFFu, hb2.v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, hb2.node, 16);
+                    hb2.take(ov, on);
+                    if (lane < 16) wb.take(hb2.v, hb2.node);
+                } else if (lane < 16) {
+                    const uint32_t v = my_best[0][lane + 1];
+                    const uint32_t nd = sl.node[0];
+                    if (v != kInf) {
+                        atomicMin(prm.best + (size_t)nd * 16 + lane, v);
+                        wb.take(v, nd);
+                    }
+                }
+            } else {
+                const bool ok = lane < live;
+                uint32_t out[16];
+#pragma unroll
+                for (int k = 0; k < 16; k++) out[k] = kInf;
+                const uint32_t node = sl.node[lane], f = sl.f[lane];
+                if (ok) {
+                    score_small_any<true>((int)p, sl.raw + sl.off[lane], f, out);
+                    uint4 *o = reinterpret_cast<uint4 *>(prm.best + (size_t)node * 16);
+                    o[0] = make_uint4(out[0], out[1], out[2], out[3]);
+                    o[1] = make_uint4(out[4], out[5], out[6], out[7]);
+                    o[2] = make_uint4(kInf, kInf, kInf, kInf);
+                    o[3] = make_uint4(kInf, kInf, kInf, kInf);
+                    if (prm.score_k) prm.scores[node] = (uint8_t)score_byte(pick_row(out, prm.score_k), prm.score_den);
+                }
+                if (prm.fold_place) {
+                    fold_small_warp4<0>(wb, out, node, lane);
+                    if (p > 4) fold_small_warp4<4>(wb, out, node, lane);
+                }
+            }
+            __syncwarp();     // every lane is done with the slot's rows and descriptor
+            if (lane == 0) mbar_arrive(&sh.empty[s]);
+        }
+        if (prm.fold_place && lane < 16 && wb.v != kInf) {
+            const unsigned long long key = ((unsigned long long)(wb.v >> 16) << 48) |
+                                           ((unsigned long long)(prm.first_node + wb.node) << 16) | (wb.v & 0xFFFFu);
+            atomicMin(&sh.place[lane], key);
+        }
+    }
+    asm volatile("griddepcontrol.launch_dependents;");
+    __syncthreads();
+    if (prm.fold_place && tid < 16 && sh.place[tid] != ~0ull) atomicMin(prm.place + tid, sh.place[tid]);
+    if (prm.seq_flag) {       // somebody reads `place` without a kernel boundary: order the folds before the count
+        __syncthreads();
+        if (tid == 0) __threadfence();
+    }
+    if (tid == 0) {           // the last CTA to finish leaves the control block zeroed for the next pass
+        const uint32_t done = atomicAdd(prm.ctl + kCtlDone, 1u);
+        if (done == gridDim.x - 1) {
+            if (!prm.keep_bins)
+                for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
+            prm.ctl[kCtlTicket] = 0u;
+            prm.ctl[kCtlDone] = 0u;
+            if (prm.seq_flag) {
+                __threadfence();
+                *reinterpret_cast<volatile unsigned long long *>(prm.seq_flag) = prm.seq;
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- multi-GPU: min-exchange of the 16 placement keys
 // One CTA per GPU on the communication stream, all GPUs of one NVLink domain (peer memory mapped through CUDA IPC).
 // Every rank stores its 16 keys into every rank's inbox, fences, raises its flag there with the exchange number, waits
@@ -600,24 +968,46 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 // rank reuses a parity only after its previous exchange on the other parity completed, i.e. after every peer has
 // entered that one -- by stream order the peers have then finished reading this parity.
 constexpr int kMaxPeers = 8;
+constexpr unsigned long long kExchangeTimeoutNs = 2000000000ull;   // a peer that does not show up within 2 s is not coming
 struct ExchangeParams {
     unsigned long long *place;            // 16 local keys in, 16 reduced keys out
     const unsigned long long *k1_flag;    // null: the stream already orders this kernel after the producer
     unsigned long long k1_val;
     unsigned long long *inbox[kMaxPeers]; // inbox base of every rank (own address for the own rank)
     unsigned long long *done_flag;        // local: exchange number written when `place` holds the result
+    unsigned long long *err_flag;         // local: exchange number of the last exchange that gave up waiting
     unsigned long long seq;               // exchange number, the same on every rank
     uint32_t rank, world, parity;
 };
+// spin until *flag >= want; false when the time is up (the waits below must never hang the GPU: ranks that issue their
+// passes in different orders, or a rank that died, end in an error on the host instead)
+__device__ __forceinline__ bool wait_flag_bounded(const unsigned long long *flag, unsigned long long want, unsigned ns)
+{
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 0;; spins++) {
+        if (*reinterpret_cast<const volatile unsigned long long *>(flag) >= want) return true;
+        __nanosleep(ns);
+        if ((spins & 255u) == 255u) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (!t0) t0 = t;
+            else if (t - t0 > kExchangeTimeoutNs) return false;
+        }
+    }
+}
 // 16 x kMaxPeers threads on purpose: measured against a one-warp version, which leaves room beside K1's five CTAs
 // per SM, sits there spinning through the whole pass and costs the scoring stream 1.3 us per pass (K1's programmatic
 // launch is slower while another grid is resident); this size only gets onto an SM once K1 drains.
 __global__ void __launch_bounds__(16 * kMaxPeers) k_exchange(ExchangeParams prm)
 {
+    __shared__ uint32_t s_late;
     const uint32_t tid = threadIdx.x, k = tid & 15u, q = tid >> 4;
-    if (tid == 0 && prm.k1_flag) {
-        while (*reinterpret_cast<const volatile unsigned long long *>(prm.k1_flag) < prm.k1_val) __nanosleep(100);
-        __threadfence();   // acquire side of K1's release (folds, fence, flag store): the reads of `place` below stay behind it
+    if (tid == 0) {
+        s_late = 0;
+        if (prm.k1_flag) {
+            if (!wait_flag_bounded(prm.k1_flag, prm.k1_val, 100)) s_late = 1;
+            __threadfence();   // acquire side of K1's release (folds, fence, flag store): the reads of `place` below stay behind it
+        }
     }
     __syncthreads();
     const uint32_t slot = prm.rank * 2 + prm.parity;
@@ -631,10 +1021,12 @@ __global__ void __launch_bounds__(16 * kMaxPeers) k_exchange(ExchangeParams prm)
     if (tid < prm.world) *reinterpret_cast<volatile unsigned long long *>(prm.inbox[tid] + flags + slot) = prm.seq;
     unsigned long long *mine = prm.inbox[prm.rank];
     if (tid < prm.world)
-        while (*reinterpret_cast<volatile unsigned long long *>(mine + flags + tid * 2 + prm.parity) < prm.seq) __nanosleep(32);
+        if (!wait_flag_bounded(mine + flags + tid * 2 + prm.parity, prm.seq, 32)) atomicOr(&s_late, 1u);
     __threadfence_system();
     __syncthreads();
-    if (tid < 16) {
+    if (s_late) {           // somebody never came: the keys stay this rank's own, the host hears about it
+        if (tid == 0) *reinterpret_cast<volatile unsigned long long *>(prm.err_flag) = prm.seq;
+    } else if (tid < 16) {
         unsigned long long m = ~0ull;
         for (uint32_t r = 0; r < prm.world; r++) {
             const unsigned long long v = *reinterpret_cast<volatile unsigned long long *>(mine + (size_t)(r * 2 + prm.parity) * 16 + tid);
@@ -909,10 +1301,12 @@ __global__ void __launch_bounds__(kCta) k_gaia_select(const TreeRow *__restrict_
 __global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict__ best, uint32_t n, uint32_t m,
                                                       uint32_t cmax, uint32_t *__restrict__ scores4,
                                                       const unsigned long long *__restrict__ place,
-                                                      unsigned long long *__restrict__ out_place)
+                                                      unsigned long long *__restrict__ out_place,
+                                                      const unsigned long long *__restrict__ xerr)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (out_place && t < 16) out_place[t] = place[t];
+    if (out_place && t == 16) out_place[16] = *xerr;     // non-zero: a min-exchange gave up on a peer
     const uint32_t i0 = t * 4;
     if (i0 >= n) return;
     const uint32_t den = cmax * (m * (m - 1) / 2);
@@ -930,6 +1324,43 @@ __global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict
         packed |= sc << (8 * q);
     }
     scores4[t] = packed;
+}
+
+// The pass already left one score byte per node on the device (ScoreParams::scores): this moves them to the host
+// reply buffer, 16 nodes per thread and one 16-byte store (`out16` may be mapped pinned host memory), filling in the
+// nodes K1 could not score on the fly (kScorePending: rows built by several work units) from the best table.
+__global__ void __launch_bounds__(kCta) k_scores_out(const uint8_t *__restrict__ scores, const uint32_t *__restrict__ best,
+                                                     uint32_t n, uint32_t m, uint32_t den, uint4 *__restrict__ out16,
+                                                     const unsigned long long *__restrict__ place,
+                                                     unsigned long long *__restrict__ out_place,
+                                                     const unsigned long long *__restrict__ xerr)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (out_place && t < 16) out_place[t] = place[t];
+    if (out_place && t == 16) out_place[16] = *xerr;     // non-zero: a min-exchange gave up on a peer
+    const uint32_t i0 = t * 16;
+    if (i0 >= n) return;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (i0 + 16 <= n) {
+        v = __ldg(reinterpret_cast<const uint4 *>(scores) + t);
+    } else {
+        uint8_t *b = reinterpret_cast<uint8_t *>(&v);
+        for (uint32_t q = 0; i0 + q < n; q++) b[q] = scores[i0 + q];
+    }
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        if (w[q] & 0x80808080u) {     // scores are 0..10: a set top bit is the pending mark
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                if (((w[q] >> (8 * r)) & 0xFFu) == kScorePending) {
+                    const uint32_t node = i0 + q * 4 + r;
+                    const uint32_t sc = node < n ? score_byte(best[(size_t)node * 16 + (m - 1)], den) : 0u;
+                    w[q] = (w[q] & ~(0xFFu << (8 * r))) | (sc << (8 * r));
+                }
+        }
+    }
+    out16[t] = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // launch-cadence probes for profiling (no work)

@@ -133,7 +133,11 @@ int gt_release(gt_ctx *ctx, const uint32_t *nodes, const uint16_t *masks, uint32
  * out_node / out_mask per event (0xFFFFFFFF / 0 when unplaceable or nothing to release).
  * The GPU scores every (topology class, free mask) once (3^n subsets per class) into a memo table and
  * the host commit loop looks rows up; with too many distinct topologies for that table (> 1 GiB), or
- * GT_FLAG_NO_MEMO, the touched node is re-scored on the GPU after every event.  No CPU scoring. */
+ * GT_FLAG_NO_MEMO, the touched node is re-scored on the GPU after every event.  No CPU scoring.
+ * On a sharded cluster (gt_comm_init) the call is collective: every rank passes the same events and gets the same
+ * outputs (global node indices).  The table is built in `world` slices, one per GPU, and gathered; the host loop --
+ * sequential by definition -- then runs replicated on every rank over the gathered node states (8 bytes per node),
+ * each rank applying the placements that land on its own shard to its tables.  No exchange per event. */
 int gt_schedule(gt_ctx *ctx, const uint8_t *ev_k, const uint32_t *ev_arg, uint32_t n_events, uint32_t *out_node,
                 uint16_t *out_mask, uint64_t *out_placed);
 
@@ -191,6 +195,14 @@ int gt_bind_annotations(uint16_t mask, int64_t assume_time, int assigned, char *
  * asking for m GPUs; re-scores whatever changed first.  out_scores: n_nodes bytes.  out_place: optional,
  * 16 placement keys (as gt_best_node for k = 1..16) fetched in the same synchronisation. */
 int gt_ext_sort(gt_ctx *ctx, uint32_t m, uint8_t *out_scores, uint64_t *out_place);
+/* The same cycle without host copies, for an extender that keeps the informer's view in pinned memory:
+ * gt_host_free returns the context's own pinned mirror of the free masks (max_nodes u16; waits for an upload that
+ * still reads it) -- write masks in place, then gt_host_free_changed(first, count) says which nodes changed (the whole
+ * shard: one bulk upload and a full pass by the next scoring call).  gt_ext_sort with out_scores == NULL leaves the
+ * reply in the mapped pinned buffer gt_host_scores returns (n_nodes bytes, valid until the next gt_ext_sort). */
+uint16_t *gt_host_free(gt_ctx *ctx);
+int gt_host_free_changed(gt_ctx *ctx, uint32_t first, uint32_t count);
+const uint8_t *gt_host_scores(gt_ctx *ctx);
 /* replaces: bindVerb "bind" design.md:100,119,223-234: choose the GPUs on `node`, commit, format annotations */
 int gt_ext_bind(gt_ctx *ctx, uint32_t node, uint32_t m, int64_t assume_time, uint16_t *out_mask,
                 char *out_annotations, size_t cap);
@@ -248,6 +260,12 @@ int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds
 /* time `iters` back-to-back launches of one kernel ("step", "step_nograph", "bin", "score", "argmin", "int32_peak") with
  * CUDA events on the context's stream; out_ms = average per launch */
 int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
+/* K0 and K1 timed launch by launch (CUDA events between the kernels) while n_ctx contexts on one device and stream take
+ * turns, so that every launch finds its tables in DRAM once the replicas exceed the L2: out_us = {K0, K1, K0+K1} */
+int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float out_us[3]);
+/* this rank's own 16 placement keys recomputed from its best table, no exchange: the min over ranks of these is what
+ * gt_best_node must return on every rank (checked by bench.py and the multi-GPU tests) */
+int gt_best_node_local(gt_ctx *ctx, uint64_t out_place[16]);
 
 /* ---- scoring without any allocation ---- */
 /* No counterpart in the reference.
@@ -287,6 +305,9 @@ int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_gpus, const 
 /* ---- multi-GPU: nodes are sharded, one context per GPU; the only exchange is a min over 16 keys ---- */
 int gt_comm_unique_id(uint8_t out_id[128]);
 int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
+/* further contexts of one process on the same device (other clusters, replicas) join the communicator of `owner`
+ * instead of creating their own; all ranks must do the same, and `owner` must be destroyed last */
+int gt_comm_share(gt_ctx *ctx, gt_ctx *owner);
 /* how the placement keys travel between ranks: 0 = no communicator, 1 = NCCL all-reduce, 2 = own kernel over peer
  * memory (ranks are separate processes on one NVLink domain that could map each other's inbox through CUDA IPC) */
 int gt_comm_mode(const gt_ctx *ctx);
