@@ -499,3 +499,41 @@ def test_gpu_matches_committed_golden_sweep(gt, oracle):
         a.load_nodes(lv, n, fr)
         a.score_all(fetch=False)
         assert (a.best_node(np.arange(1, 17, dtype=np.uint8)) == gold["config2_place"]).all()
+
+
+@pytest.mark.parametrize("config,N", [(4, 700), (4, 9000), (3, 5000), (33, 300)])
+def test_sort_scores_left_by_the_pass(gt, oracle, config, N):
+    """`sort` after a whole-shard mask update runs a full pass that leaves one score byte per node as it goes (nodes
+    whose rows several work units build are scored afterwards from the table); same bytes as the formula on the oracle's
+    table, through the copying call and through the zero-copy surface (pinned mirror in, mapped scores out)."""
+    lut = oracle.lut(0)
+    cmax = oracle.cmax(lut)
+    lv, n, fr, _ = oracle.synth_cluster(config, 0x50A7 + N, 0, N)
+    rng = np.random.RandomState(N)
+    with gt.Allocator(N) as a:
+        a.load_nodes(lv, n, fr)
+        for it, m in enumerate((1, 2, 5, 8, 11, 16, 3)):
+            cur = (fr & rng.randint(0, 1 << 16, N).astype(np.uint16)).astype(np.uint16) if it % 2 else fr
+            want_best, _ = oracle.exhaustive_cluster(lv, n, cur, lut, 4)
+            ln = m * (m - 1) // 2
+            want = np.array([0 if b == ol.INFEASIBLE else oracle.score_int(int(b) >> 16, ln, cmax) for b in want_best[:, m - 1]],
+                            np.uint8)
+            place = np.zeros(16, np.uint64)
+            if it % 3 == 2:
+                scores = np.zeros(N, np.uint8)
+                a.update_free(cur)
+                a.ext_sort_into(m, scores, place)
+            else:
+                a.host_free()[:N] = cur
+                a.host_free_changed()
+                a.ext_sort_inplace(m, place)
+                scores = a.host_scores().copy()
+            assert (scores == want).all(), (config, N, m)
+            assert (place == oracle.cluster_argmin(want_best)).all()
+            assert (a.score_all() == want_best).all()
+            # nothing changed: the next sort for another size comes from the table, not from a pass
+            m2 = 1 + (m + 3) % 16
+            a.ext_sort_inplace(m2)
+            ln2 = m2 * (m2 - 1) // 2
+            want2 = [0 if b == ol.INFEASIBLE else oracle.score_int(int(b) >> 16, ln2, cmax) for b in want_best[:, m2 - 1]]
+            assert (a.host_scores() == np.array(want2, np.uint8)).all()
