@@ -326,7 +326,7 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     if (fold && !no_pipe && n >= kPipeMinNodes) {
         int rcp = pipe_ready(c);
         if (rcp != GT_OK) return rcp;
-        cfg.gridDim = dim3(std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms));
+        cfg.gridDim = dim3(std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::pipe::kCtasPerSm));
         cfg.blockDim = dim3(gt::pipe::kCta);
         cfg.dynamicSmemBytes = sizeof(gt::pipe::Shared);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score_pipe, prm));

@@ -652,17 +652,27 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 // walks the chain ticket -> bin-list entry -> cost tiles (DRAM) -> set-up -> tree -> write-out by itself, twice per
 // pass on average, and the SM's issue slots stand idle through the first three links.  Here one CTA of 20 warps per SM
 // splits the roles: warp 0 (the producer) walks this SM's share of the units ahead of everybody else, reads their
-// bin-list entries and has the copy engine move each node's tile rows into a ring of shared-memory slots
-// (cp.async.bulk from this GPU's own cost table, one copy per node, completion counted by the slot's mbarrier); the
-// other 19 warps (consumers) take filled slots in order, run the unit out of shared memory, write its rows and hand the
-// slot back.  Units are dealt round-robin over the SMs in cost order (unit u belongs to CTA u mod gridDim.x): every SM
+// bin-list entries and streams each node's tile rows into a ring of shared-memory slots with asynchronous 16-byte
+// copies (cp.async: global -> shared without a register stop-over, their completion counted by the slot's mbarrier);
+// the other 19 warps (consumers) take filled slots in order, run the unit out of shared memory, write its rows and hand
+// the slot back.  Units are dealt round-robin over the SMs in cost order (unit u belongs to CTA u mod gridDim.x): every SM
 // gets the same number of every unit type +-1, no ticket atomics.  Slot = 4608 bytes of tile rows (16 full tiles of a
 // many-lanes-per-node unit, or 32 nodes' rows 0..highest free GPU of a one-lane-per-node unit, 16 bytes of padding
 // between nodes against bank conflicts; a unit whose rows do not fit travels as two half units) + the unit's descriptor.
 namespace pipe {
-constexpr int kWarps = 20;                 // 1 producer + 19 consumers: what 96 registers per thread leave room for
+#ifndef GT_PIPE_WARPS
+#define GT_PIPE_WARPS 20
+#endif
+#ifndef GT_PIPE_CTAS
+#define GT_PIPE_CTAS 1
+#endif
+#ifndef GT_PIPE_SLOTS
+#define GT_PIPE_SLOTS 32
+#endif
+constexpr int kWarps = GT_PIPE_WARPS;      // 1 producer + 19 consumers: what 96 registers per thread leave room for
+constexpr int kCtasPerSm = GT_PIPE_CTAS;
 constexpr int kCta = kWarps * 32;
-constexpr int kSlots = 32;
+constexpr int kSlots = GT_PIPE_SLOTS;
 constexpr int kSlotRaw = 4608;
 constexpr uint32_t kPoison = 0xFFFFFFFFu;  // descriptor of the slots that tell the consumers to stop
 constexpr int kBatch = 8;                  // units whose bin-list entries the producer has in flight together
@@ -692,10 +702,6 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_expect(unsigned long long *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
 __device__ __forceinline__ bool mbar_try(unsigned long long *bar, uint32_t parity)
 {
     uint32_t ok;
@@ -718,11 +724,17 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t pari
         }
     }
 }
-// plain (non-multicast) bulk copy, global memory of this GPU -> this CTA's shared memory
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, unsigned long long *bar)
+// 16 bytes global -> shared without a register stop-over (LDGSTS), and the arrival that fires once all of this
+// thread's earlier copies have landed.  (One bulk copy per node -- cp.async.bulk, 64-256 bytes each -- was measured
+// first: the copy engine delivered about 2 bytes per ns per SM on such small scattered pieces, 3x slower than the
+// kernel it was meant to feed: profiles/r2_ab_pipe_bulkcopy_v1.txt.)
+__device__ __forceinline__ void copy16_async(void *dst, const void *src)
 {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_after_copies(unsigned long long *bar)
+{
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 // where unit u of the pass lives: bin (hand-out order index i, advanced from the previous unit), its nodes
@@ -752,17 +764,17 @@ __device__ __forceinline__ UnitAt locate(const Shared &sh, uint32_t u, int &i)
 }
 }  // namespace pipe
 
-__global__ void __launch_bounds__(pipe::kCta, 1) k_score_pipe(ScoreParams prm)
+__global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(ScoreParams prm)
 {
     using namespace pipe;
     extern __shared__ __align__(128) uint8_t pipe_smem[];
     Shared &sh = *reinterpret_cast<Shared *>(pipe_smem);
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     if (tid == 0) {
-        for (int q = 0; q < kSlots; q++) { mbar_init(&sh.full[q], 1); mbar_init(&sh.empty[q], 1); }
+        // full: the 32 producer lanes' copies + the descriptor's release by lane 0; empty: the consumer's lane 0
+        for (int q = 0; q < kSlots; q++) { mbar_init(&sh.full[q], 33); mbar_init(&sh.empty[q], 1); }
         sh.next = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     if (tid < 16) sh.place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible
@@ -798,17 +810,28 @@ __global__ void __launch_bounds__(pipe::kCta, 1) k_score_pipe(ScoreParams prm)
         const uint32_t n_units = sh.n_units, G = gridDim.x;
         uint32_t q = 0;                 // slots filled so far (a unit takes one slot, sometimes two)
         int i_load = 0, i_use = 0;
+        // lane t describes node t of the unit (node, free mask, bytes of tile rows wanted, where they go in the slot);
+        // the copies themselves are spread over the lanes 16 bytes (one tile row) at a time: `per` lanes per node
         auto fill = [&](uint32_t p, uint32_t lu, uint32_t live, uint32_t node, uint32_t f, uint32_t bytes, uint32_t off) {
             const uint32_t s = q % kSlots;
             if (q >= (uint32_t)kSlots) mbar_wait(&sh.empty[s], ((q / kSlots) - 1u) & 1u);
             Slot &sl = sh.slot[s];
             sl.node[lane] = node; sl.f[lane] = f; sl.off[lane] = (uint16_t)off;
             if (lane == 0) { sl.p = p; sl.lu = lu; sl.live = live; }
-            const uint32_t total = __reduce_add_sync(0xFFFFFFFFu, bytes);
+            const uint32_t most = __reduce_max_sync(0xFFFFFFFFu, bytes);
+            if (most) {
+                const uint32_t per = most > 128u ? 16u : 8u;          // lanes (rows) per node and copy instruction
+                const uint32_t row = lane & (per - 1u), sub = lane / per, step = 32u / per;
+                for (uint32_t j0 = 0; j0 < live; j0 += step) {
+                    const uint32_t j = j0 + sub;                      // (j < 32 always: live <= 32, step divides 32)
+                    const uint32_t nj = __shfl_sync(0xFFFFFFFFu, node, j), bj = __shfl_sync(0xFFFFFFFFu, bytes, j);
+                    const uint32_t oj = __shfl_sync(0xFFFFFFFFu, off, j);
+                    if (row * 16u < bj) copy16_async(sl.raw + oj + row * 16u, prm.cost + (size_t)nj * 256 + row * 16u);
+                }
+            }
+            mbar_arrive_after_copies(&sh.full[s]);
             __syncwarp();
-            if (lane == 0) mbar_arrive_expect(&sh.full[s], total);
-            __syncwarp();
-            if (bytes) bulk_g2s(sl.raw + off, prm.cost + (size_t)node * 256, bytes, &sh.full[s]);
+            if (lane == 0) mbar_arrive(&sh.full[s]);      // releases the descriptor written above
             q++;
         };
         for (uint32_t j0 = 0; j0 < n_units; j0 += kBatch) {
