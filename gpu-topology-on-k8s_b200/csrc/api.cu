@@ -77,7 +77,7 @@ struct gt_ctx {
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
     uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
-    unsigned long long *d_place = nullptr;      // [4][16]: [2],[3] = the two parities of the K0+K1 path, [0] exchange warm-up
+    unsigned long long *d_place = nullptr;      // [8][16]: [1] scratch of gt_best_node_local, [2],[3] the two key buffers K1 folds into, [4],[5] the cluster-wide keys of the two latest passes (peer-memory exchange)
     unsigned long long *place_cur = nullptr;    // where the latest placement keys are
     cudaGraphExec_t step_exec[2] = {nullptr, nullptr};   // captured K0 + K1 of a full pass, per place parity
     uint32_t step_nodes = 0;                    // n_nodes the graphs were captured for
@@ -99,10 +99,10 @@ struct gt_ctx {
     std::unordered_map<std::string, std::pair<uint32_t, uint16_t>> pod_bound;    // uid -> (node, GPUs)
     unsigned long long *d_inbox = nullptr;      // own inbox: keys[world][2][16] + flags[world][2]
     unsigned long long *peer_inbox[gt::kMaxPeers] = {};
-    unsigned long long *d_xflags = nullptr;     // [0] K1's pass number, [1 + parity] number of the last finished exchange
-    uint64_t k1_seq = 0, xchg_seq = 0, parity_seq[2] = {0, 0};
-    uint64_t *xchg_seq_p = nullptr;             // the exchange counter in use: the own one, or the lender's (gt_comm_share)
-    bool comm_borrowed = false;                 // communicator, communication stream and inboxes belong to another context
+    unsigned long long *d_xflags = nullptr;     // [3]: number of a pass whose exchange gave up waiting for a peer (0 = none)
+    // peer-memory exchange (kernels.cuh exchange_step): passes whose keys travel, how far posting and reducing got
+    uint64_t x_seq = 0, x_posted = 0, x_reduced = 0;
+    bool comm_borrowed = false;                 // the NCCL communicator and the communication stream belong to another context
     uint32_t *d_ids = nullptr;
     uint16_t *d_masks = nullptr;
     uint32_t *d_peak_out = nullptr;
@@ -248,11 +248,11 @@ unsigned long long *bin_place(gt_ctx *c, uint32_t parity) { return c->d_place + 
 
 gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep_bins)
 {
-    gt::ScoreParams p;
+    gt::ScoreParams p = {};
     p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
     p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
     p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
-    p.seq_flag = nullptr; p.seq = 0;
+    p.xw = gt::XWork{};
     p.scores = nullptr; p.score_k = 0; p.score_den = 0;
     if (c->want_score_m && fold_into) {   // full pass on behalf of a `sort` call: one score byte per node on the way
         const uint32_t m = c->want_score_m;
@@ -265,8 +265,7 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
 }
 
 // K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
-int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place,
-               const unsigned long long *wait_flag = nullptr, unsigned long long wait_val = 0)
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place)
 {
     // programmatic dependent of the kernel in front of it (the previous pass's K1 in a scoring loop): the launch
     // latency between two passes is spent while that kernel still runs; K0 waits inside for its completion
@@ -281,7 +280,7 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus, (const uint16_t *)c->d_free, d_ids, n,
-                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place, wait_flag, wait_val,
+                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
                                   (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr)));
     c->launches++;
     return GT_OK;
@@ -301,7 +300,7 @@ int pipe_ready(gt_ctx *c)
     return GT_OK;
 }
 
-int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins = false, bool publish = false)
+int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins = false, const gt::XWork *xw = nullptr)
 {
     // persistent warps: every resident CTA slot, fewer when there is little work
     const uint32_t grid = std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::kScoreMinCtas);
@@ -317,13 +316,12 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     gt::ScoreParams prm = score_params(c, fold, keep_bins);
-    if (publish) {
-        prm.seq_flag = c->d_xflags;
-        prm.seq = ++c->k1_seq;
-    }
-    // full passes over enough nodes to give every SM several units: the producer / consumer form of K1 (one CTA per SM)
-    static const bool no_pipe = getenv("GT_NO_PIPE") != nullptr;   // profiling aid
-    if (fold && !no_pipe && n >= kPipeMinNodes) {
+    if (xw) prm.xw = *xw;     // multi-GPU: one warp of this K1 does the exchange work of the two passes before it
+    // GT_PIPE=1: the producer / consumer form of K1 for full passes -- same results (it passes every parity test), but
+    // its one producer warp per CTA cannot describe units as fast as the consumers finish them, so it measures 2-3x
+    // slower than k_score (profiles/r2_ab_pipe_*.txt) and stays an experiment
+    static const bool use_pipe = getenv("GT_PIPE") != nullptr;
+    if (fold && use_pipe && n >= kPipeMinNodes) {
         int rcp = pipe_ready(c);
         if (rcp != GT_OK) return rcp;
         cfg.gridDim = dim3(std::min<uint32_t>(n / 8 + gt::kBins, (uint32_t)c->num_sms * gt::pipe::kCtasPerSm));
@@ -352,43 +350,83 @@ int launch_singular(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long 
     return GT_OK;
 }
 
-// Multi-GPU: min of the 16 placement keys over all ranks, on the communication stream; consumers wait for
-// ev_comm[parity].  With peer memory (c->p2p) this is k_exchange; `flag_ordered`: the producer was a K1 launched with
-// publish = true, the kernel waits for its flag itself and nothing is put between K1 and the next K0 on the scoring
-// stream (an event record there would cost the next K0 its programmatic launch).  Otherwise, and always on the NCCL
-// fallback, the pass that produced `place` is ordered before the exchange by an event.
-int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity, bool flag_ordered)
+// Multi-GPU without peer memory (ranks that cannot map each other's memory, more than 8 ranks, GT_NO_P2P): min of the
+// 16 placement keys over all ranks as an NCCL all-reduce on the communication stream, ordered behind the pass by an
+// event; consumers wait for ev_comm[parity].
+int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity)
 {
-    if (!c->comm) return GT_OK;
-    if (!(c->p2p && flag_ordered)) {
-        GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
-        GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
-    }
-    if (c->p2p) {
-        gt::ExchangeParams prm = {};
-        prm.place = place;
-        prm.k1_flag = flag_ordered ? c->d_xflags : nullptr;
-        prm.k1_val = c->k1_seq;
-        for (int q = 0; q < c->world; q++) prm.inbox[q] = c->peer_inbox[q];
-        prm.done_flag = c->d_xflags + 1 + parity;
-        prm.err_flag = c->d_xflags + 3;
-        prm.seq = ++*c->xchg_seq_p;
-        // inbox slots alternate with the exchange number, which every rank counts alike; the local key-buffer parity
-        // may drift between ranks (a rank-local gt_time_kernel runs passes the others do not)
-        prm.rank = (uint32_t)c->rank; prm.world = (uint32_t)c->world; prm.parity = (uint32_t)(prm.seq & 1u);
-        gt::k_exchange<<<1, 16 * gt::kMaxPeers, 0, c->comm_stream>>>(prm);
-        c->launches++;
-        GT_CUDA(c, cudaGetLastError());
-        c->parity_seq[parity] = prm.seq;
-    } else {
-        NcclApi *api = nccl_api();
-        int e = api->AllReduce(place, place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
-        if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
-    }
+    if (!c->comm || c->p2p) return GT_OK;
+    GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
+    GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
+    NcclApi *api = nccl_api();
+    int e = api->AllReduce(place, place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
+    if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce: %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     GT_CUDA(c, cudaEventRecord(c->ev_comm[parity], c->comm_stream));
     c->comm_used[parity] = true;
     c->comm_last = (int)parity;
     return GT_OK;
+}
+
+// ---- Multi-GPU over peer memory: the exchange is piggybacked on the passes (kernels.cuh, exchange_step).
+// Key buffers of pass number s: this rank's own keys (what K1 folds into) and the cluster-wide result.
+unsigned long long *x_local(gt_ctx *c, uint64_t s) { return c->d_place + 32 + 16 * (s & 1u); }
+unsigned long long *x_global(gt_ctx *c, uint64_t s) { return c->d_place + 64 + 16 * (s & 1u); }
+bool lazy_exchange(const gt_ctx *c) { return c->comm && c->p2p; }
+
+gt::XWork x_blank(gt_ctx *c)
+{
+    gt::XWork w = {};
+    for (int q = 0; q < c->world; q++) w.inbox[q] = c->peer_inbox[q];
+    w.err_flag = c->d_xflags + 3;
+    w.rank = (uint32_t)c->rank;
+    w.world = 0;          // set once there is work
+    return w;
+}
+
+// the exchange work that goes with pass s: reduce(s-2), then post(s-1)
+gt::XWork x_step_for_pass(gt_ctx *c, uint64_t s)
+{
+    gt::XWork w = x_blank(c);
+    if (s >= 3 && c->x_reduced < s - 2) {
+        w.seq_reduce1 = s - 2; w.out1 = x_global(c, s - 2);
+        c->x_reduced = s - 2;
+        w.world = (uint32_t)c->world;
+    }
+    if (s >= 2 && c->x_posted < s - 1) {
+        w.seq_post = s - 1; w.post_keys = x_local(c, s - 1);
+        c->x_posted = s - 1;
+        w.world = (uint32_t)c->world;
+    }
+    return w;
+}
+
+int launch_exchange_step(gt_ctx *c, const gt::XWork &w)
+{
+    if (!w.world) return GT_OK;
+    gt::k_exchange_step<<<1, 32, 0, c->stream>>>(w);
+    c->launches++;
+    GT_CUDA(c, cudaGetLastError());
+    return GT_OK;
+}
+
+// somebody wants the cluster-wide keys of the latest pass: whatever of reduce(L-1), post(L), reduce(L) is still open
+int x_consume(gt_ctx *c)
+{
+    const uint64_t L = c->x_seq;
+    if (!L || c->x_reduced >= L) return GT_OK;
+    gt::XWork w = x_blank(c);
+    w.world = (uint32_t)c->world;
+    if (L >= 2 && c->x_reduced < L - 1) { w.seq_reduce1 = L - 1; w.out1 = x_global(c, L - 1); }
+    if (c->x_posted < L) { w.seq_post = L; w.post_keys = x_local(c, L); }
+    w.seq_reduce2 = L; w.out2 = x_global(c, L);
+    c->x_posted = c->x_reduced = L;
+    return launch_exchange_step(c, w);
+}
+
+// where the placement keys a caller may see are: the cluster-wide ones with peers, else what the pass left
+const unsigned long long *cluster_keys(gt_ctx *c)
+{
+    return lazy_exchange(c) && c->x_seq ? x_global(c, c->x_seq) : c->place_cur;
 }
 
 // an exchange kernel gave up waiting for a peer (kernels.cuh, kExchangeTimeoutNs): the placement keys of this context
@@ -399,12 +437,10 @@ int exchange_failed(gt_ctx *c)
                                  "ranks issued the passes of their contexts in different orders%s");
 }
 
-// before a pass overwrites place[parity]: the exchange that last used that buffer must be finished.
-// in_kernel: K0 itself waits for the exchange's done flag (launch_bin's wait_flag), nothing goes into the stream.
-int wait_place_free(gt_ctx *c, uint32_t parity, bool in_kernel)
+// NCCL fallback: before a pass overwrites place[parity] the all-reduce that last used that buffer must be finished
+int wait_place_free(gt_ctx *c, uint32_t parity)
 {
-    if (c->comm && c->comm_used[parity] && !(c->p2p && in_kernel))
-        GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[parity], 0));
+    if (c->comm && !c->p2p && c->comm_used[parity]) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[parity], 0));
     return GT_OK;
 }
 
@@ -447,9 +483,8 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
     return GT_OK;
 }
 
-int launch_argmin(gt_ctx *c)
+int launch_argmin(gt_ctx *c, unsigned long long *place)
 {
-    unsigned long long *place = bin_place(c, c->bin_parity);
     GT_CUDA(c, cudaMemsetAsync(place, 0xFF, 16 * sizeof(unsigned long long), c->stream));
     const size_t quarters = (size_t)c->n_nodes * 4;      // 16-byte pieces; 8 per thread
     const uint32_t grid = (uint32_t)std::min<size_t>((quarters + gt::kCta * 8 - 1) / (gt::kCta * 8), (size_t)c->num_sms * 4);
@@ -504,13 +539,17 @@ int launch_memo_pass(gt_ctx *c, unsigned long long *place)
 int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
 {
     int rc;
-    const uint32_t par = c->bin_parity;
     const bool memo_pass = !d_ids && n && (c->flags & GT_FLAG_MEMO_PASS) && !c->memo_pass_failed;
     const bool graph = !d_ids && n && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed;
-    // plain K0 -> K1 pass with peers: all cross-stream ordering through device flags (see exchange_min)
-    bool flagged = c->comm && c->p2p && !d_ids && n && !memo_pass && !graph && c->k1_policy == GT_K1_FIRST_UNUSED;
-    if ((rc = wait_place_free(c, par, flagged)) != GT_OK) return rc;
+    // with peers over peer memory the pass has a number, its key buffers go by that number, and the exchange work of
+    // the two passes before it rides on its K1 (or, on the paths without a K1 of their own, in a one-warp kernel)
+    const bool lazy = lazy_exchange(c);
+    const uint64_t seq = lazy ? c->x_seq + 1 : 0;
+    gt::XWork step = lazy ? x_step_for_pass(c, seq) : gt::XWork{};
+    const uint32_t par = lazy ? (uint32_t)(seq & 1u) : c->bin_parity;
+    if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
     c->scores_m = 0;
+    bool step_taken = false;
     if (!d_ids && n) {
         bool done = false;
         if (memo_pass) {
@@ -524,15 +563,11 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
             if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
         }
         if (!done) {
-            // flagged: K0's block 0 itself waits for the exchange that last used this key buffer before presetting it
-            const bool wait_in_k0 = flagged && c->comm_used[par];
-            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par), wait_in_k0 ? c->d_xflags + 1 + par : nullptr,
-                                 c->parity_seq[par])) != GT_OK) return rc;
-            if ((rc = launch_score(c, n, bin_place(c, par), false, flagged)) != GT_OK) return rc;
+            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, bin_place(c, par), false, step.world ? &step : nullptr)) != GT_OK) return rc;
+            step_taken = true;
             if ((rc = launch_singular(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
             c->scores_m = c->want_score_m;
-        } else {
-            flagged = false;
         }
     } else {
         if (n) {
@@ -540,9 +575,11 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
             if ((rc = launch_score(c, n, nullptr)) != GT_OK) return rc;
             if ((rc = launch_singular(c, d_ids, n, nullptr)) != GT_OK) return rc;
         }
-        if ((rc = launch_argmin(c)) != GT_OK) return rc;
+        if ((rc = launch_argmin(c, bin_place(c, par))) != GT_OK) return rc;
     }
-    if ((rc = exchange_min(c, c->place_cur, par, flagged)) != GT_OK) return rc;
+    if (!step_taken && (rc = launch_exchange_step(c, step)) != GT_OK) return rc;
+    if (lazy) c->x_seq = seq;
+    else if ((rc = exchange_min(c, c->place_cur, par)) != GT_OK) return rc;
     c->bin_parity ^= 1u;
     c->best_valid = true;
     c->place_valid = true;
@@ -585,7 +622,6 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
     gt_ctx *c = new (std::nothrow) gt_ctx();
     if (!c) return GT_ERR_NOMEM;
     c->err[0] = 0;
-    c->xchg_seq_p = &c->xchg_seq;
     c->device = cfg->device;
     c->cap = cfg->max_nodes;
     c->first_node = cfg->first_node;
@@ -615,8 +651,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_free, (size_t)gt::kBins * N * sizeof(uint16_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMalloc(&c->d_place, 64 * sizeof(unsigned long long)));
-        GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 64 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMalloc(&c->d_place, 128 * sizeof(unsigned long long)));
+        GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 128 * sizeof(unsigned long long)));
         c->place_cur = c->d_place + 32;
         GT_CUDA(c, cudaMalloc(&c->d_ids, N * 4));
         GT_CUDA(c, cudaMalloc(&c->d_masks, N * 2));
@@ -675,7 +711,7 @@ void gt_destroy(gt_ctx *c)
     cudaFree(c->d_free); cudaFree(c->d_best); cudaFree(c->d_bin_cnt); cudaFree(c->d_bin_list); cudaFree(c->d_bin_free); cudaFree(c->d_memo); cudaFree(c->d_row0); cudaFree(c->d_node_class); cudaFree(c->d_place);
     cudaFree(c->d_tree); cudaFree(c->d_gaia_out);
     for (int q = 0; q < gt::kMaxPeers; q++)
-        if (!c->comm_borrowed && c->peer_inbox[q] && c->peer_inbox[q] != c->d_inbox) cudaIpcCloseMemHandle(c->peer_inbox[q]);
+        if (c->peer_inbox[q] && c->peer_inbox[q] != c->d_inbox) cudaIpcCloseMemHandle(c->peer_inbox[q]);
     cudaFree(c->d_inbox); cudaFree(c->d_xflags);
     cudaFree(c->d_ids); cudaFree(c->d_masks); cudaFree(c->d_peak_out); cudaFree(c->d_scores); cudaFreeHost(c->h_scores); cudaFreeHost(c->h_place_map);
     cudaFreeHost(c->h_free); cudaFreeHost(c->h_ngpus); cudaFreeHost(c->h_ids); cudaFreeHost(c->h_masks);
@@ -923,8 +959,13 @@ int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place
         int rc = enqueue_scoring(c, nullptr, 0);
         if (rc != GT_OK) return rc;
     }
-    if (c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
-    GT_CUDA(c, cudaMemcpyAsync(c->h_place, c->place_cur, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    if (lazy_exchange(c)) {
+        int rc = x_consume(c);
+        if (rc != GT_OK) return rc;
+    } else if (c->comm && c->comm_last >= 0) {
+        GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
+    }
+    GT_CUDA(c, cudaMemcpyAsync(c->h_place, cluster_keys(c), 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     if (c->comm && c->p2p)
         GT_CUDA(c, cudaMemcpyAsync(c->h_place + 16, c->d_xflags + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -979,6 +1020,8 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
         explicit CommOff(gt_ctx *x) : c(x), saved(x->comm) { x->comm = nullptr; }
         ~CommOff() { c->comm = saved; c->place_valid = false; }
     } comm_off(c);
+    if (comm_off.saved && c->p2p && c->x_reduced < c->x_seq)    // these passes reuse the key buffers of the last two passes
+        return fail(c, GT_ERR_STATE, "gt_time_kernel: the keys of the last pass were not exchanged yet: gt_best_node on every rank first%s");
     if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));   // no exchange may still be reading the key buffers
     int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
     if (rc != GT_OK) return rc;
@@ -994,7 +1037,7 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
             return launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
         }
         if (w == "score") return launch_score(c, c->n_nodes, bin_place(c, 0), true);
-        if (w == "argmin") return launch_argmin(c);
+        if (w == "argmin") return launch_argmin(c, bin_place(c, c->bin_parity));
         if (w == "step") return enqueue_scoring(c, nullptr, c->n_nodes);
         if (w == "step_nograph") {
             int r2 = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
@@ -1050,6 +1093,8 @@ int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float ou
     int rc = GT_OK;
     for (uint32_t i = 0; i < n_ctx && rc == GT_OK; i++) {
         gt_ctx *c = ctxs[i];
+        if (lazy_exchange(c) && c->x_reduced < c->x_seq)
+            return fail(c0, GT_ERR_STATE, "gt_time_pass_rotated: keys of the last pass not exchanged yet: gt_best_node on every rank first%s");
         if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
         rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
         clear_dirty(c);
@@ -1184,13 +1229,6 @@ int setup_peer_exchange(gt_ctx *c)
     GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     GT_CUDA(c, cudaMemcpy(&ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost));
     c->p2p = ok != 0;
-    if (!c->p2p) return GT_OK;
-    // one exchange now: first touch of the peer mappings happens before any timed pass
-    int rc = exchange_min(c, c->d_place, 0, false);
-    if (rc != GT_OK) return rc;
-    GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
-    c->comm_used[0] = false;
-    c->comm_last = -1;
     return GT_OK;
 }
 
@@ -1239,10 +1277,10 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     return setup_peer_exchange(c);
 }
 
-// A second context of the same process and device joins the communicator of `owner` instead of setting up its own
-// (one NCCL communicator and one set of peer inboxes per process is enough: the exchanges of all sharing contexts run
-// one after the other on the device's communication stream and count one common exchange number).  Every rank must
-// share the same way and issue the passes of its contexts in the same order.  `owner` must outlive `c`.
+// A second context of the same process and device joins the NCCL communicator (and the communication stream) of
+// `owner` instead of creating its own -- communicator set-up is the slow part; its inbox for the peer-memory exchange
+// is its own, so its passes and exchanges are independent of the owner's.  Collective: every rank shares the same
+// way, in the same order.  `owner` must outlive `c`.
 int gt_comm_share(gt_ctx *c, gt_ctx *owner)
 {
     if (!c || !owner || c == owner) return GT_ERR_INVALID;
@@ -1250,19 +1288,17 @@ int gt_comm_share(gt_ctx *c, gt_ctx *owner)
     if (!owner->comm) return fail(c, GT_ERR_STATE, "gt_comm_share: the lending context has no communicator%s");
     if (owner->device != c->device) return fail(c, GT_ERR_INVALID, "gt_comm_share: contexts on different devices%s");
     GT_CUDA(c, cudaSetDevice(c->device));
+    GT_CUDA(c, cudaStreamSynchronize(owner->comm_stream));
     c->comm = owner->comm;
     c->comm_borrowed = true;
     c->rank = owner->rank;
     c->world = owner->world;
     c->comm_stream = owner->comm_stream;
     c->own_comm_stream = false;
-    c->p2p = owner->p2p;
-    for (int q = 0; q < gt::kMaxPeers; q++) c->peer_inbox[q] = owner->peer_inbox[q];
-    c->xchg_seq_p = owner->xchg_seq_p;
     GT_CUDA(c, cudaEventCreateWithFlags(&c->ev_pass, cudaEventDisableTiming));
     for (auto &ev : c->ev_comm) GT_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     c->place_valid = false;
-    return GT_OK;
+    return setup_peer_exchange(c);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1625,17 +1661,22 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     if (rc != GT_OK) return rc;
     if (!c->n_nodes) return GT_OK;
     const uint32_t cmax = gt_lut_cmax(c->lut);
-    if (out_place && c->comm && c->comm_last >= 0) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
+    if (out_place && lazy_exchange(c)) {
+        if ((rc = x_consume(c)) != GT_OK) return rc;
+    } else if (out_place && c->comm && c->comm_last >= 0) {
+        GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
+    }
+    const unsigned long long *keys = out_place ? cluster_keys(c) : c->place_cur;
     // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them
     if (c->scores_m == m) {
         const uint32_t threads = (c->n_nodes + 15) / 16;
         gt::k_scores_out<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
             c->d_scores, c->d_best, c->n_nodes, m, cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map),
-            c->place_cur, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+            keys, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
     } else {
         const uint32_t threads = (c->n_nodes + 3) / 4;
         gt::k_sort_scores<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-            c->d_best, c->n_nodes, m, cmax, c->d_scores_map, c->place_cur, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+            c->d_best, c->n_nodes, m, cmax, c->d_scores_map, keys, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
     }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
@@ -1913,11 +1954,10 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr, nullptr, 0ull, nullptr);
-    gt::ScoreParams prm;
+                                                                     nullptr, nullptr);
+    gt::ScoreParams prm = {};
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;
-    prm.seq_flag = nullptr; prm.seq = 0;
     prm.scores = nullptr; prm.score_k = 0; prm.score_den = 0;
     const uint32_t grid = std::min<uint32_t>(n_nodes / 8 + gt::kBins, (uint32_t)sms * gt::kScoreMinCtas);
     gt::k_score<<<grid, gt::kScoreCta, 0, s>>>(prm);

@@ -44,6 +44,17 @@ constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 
 constexpr int kStageBytes = (GT_SMALL_SMEM ? 32 : kTilesPerWarp) * kTileStride;   // staging buffer of a warp: 16 full tiles (32 for small units)
 constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
 
+// Multi-GPU: one step of the min-exchange of the 16 placement keys over peer memory (see exchange_step below).
+constexpr int kMaxPeers = 8;
+struct XWork {
+    unsigned long long *inbox[kMaxPeers];   // inbox base of every rank (own address for the own rank); world == 0: no work
+    const unsigned long long *post_keys;    // this rank's 16 keys of pass `seq_post`
+    unsigned long long *out1, *out2;        // where the cluster-wide keys of passes seq_reduce1 / seq_reduce2 go
+    unsigned long long *err_flag;           // pass number of a reduction that gave up waiting for a peer
+    unsigned long long seq_reduce1, seq_post, seq_reduce2;   // 0 = nothing to do
+    uint32_t rank, world;
+};
+
 struct ScoreParams {
     const uint8_t *cost;      // [N][256] u8 pair cost, row-major 16x16
     uint32_t *best;           // [N][16]
@@ -55,8 +66,7 @@ struct ScoreParams {
     uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
-    unsigned long long *seq_flag;   // multi-GPU: the last CTA publishes `seq` here once every fold into `place` is done
-    unsigned long long seq;         // (k_exchange on the communication stream waits for it; null = nobody waits)
+    XWork xw;                       // multi-GPU: exchange work of the two passes before this one, done by one warp of K1
     uint8_t *scores;                // `sort` verb inside the pass: HostPriority score 0..10 of every node for request size
     uint32_t score_k, score_den;    // score_k (1..16; 0 = off), den = cmax * C(score_k, 2); see score_byte()
 #ifdef GT_TRACE
@@ -108,6 +118,82 @@ __device__ __forceinline__ int bin_order(int i)
     return (int)(((i < 12) ? (lo >> (5 * i)) : (hi >> (5 * (i - 12)))) & 31ull);
 }
 
+// ---------------------------------------------------------------- multi-GPU: min-exchange of the 16 placement keys
+constexpr unsigned long long kExchangeTimeoutNs = 2000000000ull;   // a peer that does not show up within 2 s is not coming
+// spin until *flag >= want; false when the time is up (the waits below must never hang the GPU: ranks that issue their
+// passes in different orders, or a rank that died, end in an error on the host instead)
+__device__ __forceinline__ bool wait_flag_bounded(const unsigned long long *flag, unsigned long long want, unsigned ns)
+{
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 0;; spins++) {
+        if (*reinterpret_cast<const volatile unsigned long long *>(flag) >= want) return true;
+        __nanosleep(ns);
+        if ((spins & 255u) == 255u) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (!t0) t0 = t;
+            else if (t - t0 > kExchangeTimeoutNs) return false;
+        }
+    }
+}
+
+// The exchange, one warp, no kernel of its own in a loop of passes.  Every rank owns an inbox that all peers have
+// mapped (CUDA IPC): keys[world][2][16] then flags[world][2], slot parity = pass number & 1.
+//   post(s):   store this rank's 16 keys of pass s into slot [rank][s & 1] of every rank's inbox, fence, then raise
+//              the flag beside them to s (the flag is how a reader knows the keys are there);
+//   reduce(s): wait until the flags of all ranks in the own inbox show s, take the minimum of the world x 16 keys.
+// A pass's keys are final when its K1 has finished, so K1 of pass s carries reduce(s-2) and post(s-1) -- in that
+// order -- in one warp of its first CTA: the NVLink round trips disappear behind 10 us of scoring, nothing extra is
+// launched and nothing waits on the scoring stream.  Whoever wants the keys of the latest pass L runs the same step as
+// a one-warp kernel: reduce(L-1), post(L), reduce(L) (k_exchange_step).  Slot reuse is safe without credits: a rank
+// overwrites slot s & 1 with post(s) only after its own reduce(s-1), i.e. after it saw every peer's post(s-1), which
+// each peer issued after its own reduce(s-2) -- the last reader of the slot's previous content.  The same chain keeps
+// the ranks within a pass of each other.  Waits are bounded; a rank that gives up reports it through err_flag.
+__device__ __forceinline__ void exchange_step(const XWork &w, uint32_t lane)
+{
+    unsigned long long *mine = w.inbox[w.rank];
+    const size_t flags = (size_t)w.world * 32;
+    auto reduce = [&](unsigned long long seq, unsigned long long *out) {
+        if (!seq) return;
+        const uint32_t par = (uint32_t)(seq & 1u);
+        bool ok = true;
+        if (lane < w.world) ok = wait_flag_bounded(mine + flags + lane * 2 + par, seq, 32);
+        if (!__all_sync(0xFFFFFFFFu, ok)) {
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long *>(w.err_flag) = seq;
+            return;
+        }
+        __threadfence_system();      // acquire: the keys are read after the flags were seen
+        if (lane < 16) {
+            unsigned long long m = ~0ull;
+            for (uint32_t r = 0; r < w.world; r++) {
+                const unsigned long long v = *reinterpret_cast<volatile unsigned long long *>(mine + (size_t)(r * 2 + par) * 16 + lane);
+                m = v < m ? v : m;
+            }
+            out[lane] = m;
+        }
+    };
+    reduce(w.seq_reduce1, w.out1);
+    if (w.seq_post) {
+        const uint32_t slot = w.rank * 2 + (uint32_t)(w.seq_post & 1u);
+        if (lane < 16) {
+            const unsigned long long key = w.post_keys[lane];
+            for (uint32_t q = 0; q < w.world; q++)
+                *reinterpret_cast<volatile unsigned long long *>(w.inbox[q] + (size_t)slot * 16 + lane) = key;
+        }
+        __threadfence_system();      // release: keys before flags, on every peer
+        __syncwarp();
+        if (lane < w.world) *reinterpret_cast<volatile unsigned long long *>(w.inbox[lane] + flags + slot) = w.seq_post;
+    }
+    reduce(w.seq_reduce2, w.out2);
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(32) k_exchange_step(XWork w)
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    exchange_step(w, threadIdx.x);
+}
+
 // HostPriority score of a best-table entry (design.md:205-217): floor(10 * (den - cost) / den), den = cmax * C(m,2);
 // a single GPU (den = 0) scores 10, an infeasible node 0.  kScorePending marks nodes whose rows several work units
 // build together (p >= 14): k_scores_out computes their score once the pass is over.
@@ -153,9 +239,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               const uint32_t *__restrict__ ids, uint32_t n, uint32_t cap,
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
-                                              unsigned long long *__restrict__ place,
-                                              const unsigned long long *wait_flag, unsigned long long wait_val,
-                                              uint8_t *__restrict__ scores)
+                                              unsigned long long *__restrict__ place, uint8_t *__restrict__ scores)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
@@ -169,15 +253,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 #ifdef GT_TRACE
     if (tid == 0) GT_KT_MIN(5, gt_now());
 #endif
-    if (place && blockIdx.x == 0 && tid < 16) {
-        // multi-GPU: the exchange that last used this key buffer (two passes ago) must have finished with it
-        if (wait_flag) {
-            // (the exchange kernel sets its flag even when it gave up on a peer, so this ends within its time limit)
-            while (*reinterpret_cast<const volatile unsigned long long *>(wait_flag) < wait_val) __nanosleep(64);
-            __threadfence();   // acquire side of the exchange kernel's release (fence + flag store)
-        }
-        place[tid] = ~0ull;
-    }
+    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
     int p = -1;
@@ -536,6 +612,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once -- that stalled every
     // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
     const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
+    if (prm.xw.world && blockIdx.x == 0 && warp == kScoreCta / 32 - 1) exchange_step(prm.xw, lane);   // multi-GPU, see there
     uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
     int i = 0;
     WarpBest wb;
@@ -620,10 +697,6 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     __syncthreads();
     GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
-    if (prm.seq_flag) {       // somebody reads `place` without a kernel boundary: order the folds before the count
-        __syncthreads();
-        if (tid == 0) __threadfence();
-    }
     // the last CTA to finish leaves the control block zeroed for the next pass
     if (tid == 0) {
 #ifdef GT_TRACE
@@ -639,10 +712,6 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
             prm.ctl[kCtlDone] = 0u;
-            if (prm.seq_flag) {
-                __threadfence();
-                *reinterpret_cast<volatile unsigned long long *>(prm.seq_flag) = prm.seq;
-            }
         }
     }
 }
@@ -819,14 +888,25 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
             sl.node[lane] = node; sl.f[lane] = f; sl.off[lane] = (uint16_t)off;
             if (lane == 0) { sl.p = p; sl.lu = lu; sl.live = live; }
             const uint32_t most = __reduce_max_sync(0xFFFFFFFFu, bytes);
+            // 8 lanes (rows) per node, 4 nodes per copy instruction; straight-line so that the shuffles overlap
+            const uint32_t row = lane & 7u, sub = lane >> 3;
             if (most) {
-                const uint32_t per = most > 128u ? 16u : 8u;          // lanes (rows) per node and copy instruction
-                const uint32_t row = lane & (per - 1u), sub = lane / per, step = 32u / per;
-                for (uint32_t j0 = 0; j0 < live; j0 += step) {
-                    const uint32_t j = j0 + sub;                      // (j < 32 always: live <= 32, step divides 32)
+#pragma unroll
+                for (int it = 0; it < 8; it++) {
+                    const uint32_t j = (uint32_t)it * 4u + sub;
                     const uint32_t nj = __shfl_sync(0xFFFFFFFFu, node, j), bj = __shfl_sync(0xFFFFFFFFu, bytes, j);
                     const uint32_t oj = __shfl_sync(0xFFFFFFFFu, off, j);
                     if (row * 16u < bj) copy16_async(sl.raw + oj + row * 16u, prm.cost + (size_t)nj * 256 + row * 16u);
+                }
+            }
+            if (most > 128u) {      // rows 8..15 of the nodes that have them
+#pragma unroll
+                for (int it = 0; it < 8; it++) {
+                    const uint32_t j = (uint32_t)it * 4u + sub;
+                    const uint32_t nj = __shfl_sync(0xFFFFFFFFu, node, j), bj = __shfl_sync(0xFFFFFFFFu, bytes, j);
+                    const uint32_t oj = __shfl_sync(0xFFFFFFFFu, off, j);
+                    if ((row + 8u) * 16u < bj)
+                        copy16_async(sl.raw + oj + (row + 8u) * 16u, prm.cost + (size_t)nj * 256 + (row + 8u) * 16u);
                 }
             }
             mbar_arrive_after_copies(&sh.full[s]);
@@ -883,6 +963,7 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
     } else {
         // ------------------------------------------------ consumers
         uint32_t (*my_best)[kBins] = sh.best[warp];
+        if (prm.xw.world && blockIdx.x == 0 && warp == 1) exchange_step(prm.xw, lane);   // multi-GPU, see there
         for (;;) {
             uint32_t q = 0;
             if (lane == 0) q = atomicAdd(&sh.next, 1u);
@@ -962,10 +1043,6 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
     asm volatile("griddepcontrol.launch_dependents;");
     __syncthreads();
     if (prm.fold_place && tid < 16 && sh.place[tid] != ~0ull) atomicMin(prm.place + tid, sh.place[tid]);
-    if (prm.seq_flag) {       // somebody reads `place` without a kernel boundary: order the folds before the count
-        __syncthreads();
-        if (tid == 0) __threadfence();
-    }
     if (tid == 0) {           // the last CTA to finish leaves the control block zeroed for the next pass
         const uint32_t done = atomicAdd(prm.ctl + kCtlDone, 1u);
         if (done == gridDim.x - 1) {
@@ -973,10 +1050,6 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
             prm.ctl[kCtlDone] = 0u;
-            if (prm.seq_flag) {
-                __threadfence();
-                *reinterpret_cast<volatile unsigned long long *>(prm.seq_flag) = prm.seq;
-            }
         }
     }
 }
@@ -990,78 +1063,6 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
 // Inbox (u64 words): keys[world][2 parities][16], then flags[world][2].  Parities alternate with the exchange number, and a
 // rank reuses a parity only after its previous exchange on the other parity completed, i.e. after every peer has
 // entered that one -- by stream order the peers have then finished reading this parity.
-constexpr int kMaxPeers = 8;
-constexpr unsigned long long kExchangeTimeoutNs = 2000000000ull;   // a peer that does not show up within 2 s is not coming
-struct ExchangeParams {
-    unsigned long long *place;            // 16 local keys in, 16 reduced keys out
-    const unsigned long long *k1_flag;    // null: the stream already orders this kernel after the producer
-    unsigned long long k1_val;
-    unsigned long long *inbox[kMaxPeers]; // inbox base of every rank (own address for the own rank)
-    unsigned long long *done_flag;        // local: exchange number written when `place` holds the result
-    unsigned long long *err_flag;         // local: exchange number of the last exchange that gave up waiting
-    unsigned long long seq;               // exchange number, the same on every rank
-    uint32_t rank, world, parity;
-};
-// spin until *flag >= want; false when the time is up (the waits below must never hang the GPU: ranks that issue their
-// passes in different orders, or a rank that died, end in an error on the host instead)
-__device__ __forceinline__ bool wait_flag_bounded(const unsigned long long *flag, unsigned long long want, unsigned ns)
-{
-    unsigned long long t0 = 0;
-    for (uint32_t spins = 0;; spins++) {
-        if (*reinterpret_cast<const volatile unsigned long long *>(flag) >= want) return true;
-        __nanosleep(ns);
-        if ((spins & 255u) == 255u) {
-            unsigned long long t;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            if (!t0) t0 = t;
-            else if (t - t0 > kExchangeTimeoutNs) return false;
-        }
-    }
-}
-// 16 x kMaxPeers threads on purpose: measured against a one-warp version, which leaves room beside K1's five CTAs
-// per SM, sits there spinning through the whole pass and costs the scoring stream 1.3 us per pass (K1's programmatic
-// launch is slower while another grid is resident); this size only gets onto an SM once K1 drains.
-__global__ void __launch_bounds__(16 * kMaxPeers) k_exchange(ExchangeParams prm)
-{
-    __shared__ uint32_t s_late;
-    const uint32_t tid = threadIdx.x, k = tid & 15u, q = tid >> 4;
-    if (tid == 0) {
-        s_late = 0;
-        if (prm.k1_flag) {
-            if (!wait_flag_bounded(prm.k1_flag, prm.k1_val, 100)) s_late = 1;
-            __threadfence();   // acquire side of K1's release (folds, fence, flag store): the reads of `place` below stay behind it
-        }
-    }
-    __syncthreads();
-    const uint32_t slot = prm.rank * 2 + prm.parity;
-    if (q < prm.world) {
-        const unsigned long long key = *reinterpret_cast<volatile unsigned long long *>(prm.place + k);
-        *reinterpret_cast<volatile unsigned long long *>(prm.inbox[q] + (size_t)slot * 16 + k) = key;
-    }
-    __threadfence_system();
-    __syncthreads();
-    const size_t flags = (size_t)prm.world * 32;
-    if (tid < prm.world) *reinterpret_cast<volatile unsigned long long *>(prm.inbox[tid] + flags + slot) = prm.seq;
-    unsigned long long *mine = prm.inbox[prm.rank];
-    if (tid < prm.world)
-        if (!wait_flag_bounded(mine + flags + tid * 2 + prm.parity, prm.seq, 32)) atomicOr(&s_late, 1u);
-    __threadfence_system();
-    __syncthreads();
-    if (s_late) {           // somebody never came: the keys stay this rank's own, the host hears about it
-        if (tid == 0) *reinterpret_cast<volatile unsigned long long *>(prm.err_flag) = prm.seq;
-    } else if (tid < 16) {
-        unsigned long long m = ~0ull;
-        for (uint32_t r = 0; r < prm.world; r++) {
-            const unsigned long long v = *reinterpret_cast<volatile unsigned long long *>(mine + (size_t)(r * 2 + prm.parity) * 16 + tid);
-            m = v < m ? v : m;
-        }
-        prm.place[tid] = m;
-        __threadfence();
-    }
-    __syncthreads();
-    if (tid == 0) *reinterpret_cast<volatile unsigned long long *>(prm.done_flag) = prm.seq;
-}
-
 // ---------------------------------------------------------------- K2: best node per k
 // place[16] must hold ~0 (or a previous partial minimum) on entry.  Each thread reads whole 16-byte
 // quarters of rows, so its four k are fixed: k = 4*(tid&3) + {1,2,3,4}.

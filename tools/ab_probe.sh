@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B several builds inside one GPU session, three rounds.  Entries: lib.so[,ENV=VAL...]
-#   tools/ab_probe.sh "ab/base.so,GT_NO_PIPE=1 gpu-topology-on-k8s_b200/libgputopo.so" [scale_probe args]
+#   tools/ab_probe.sh "ab/base.so,gpu-topology-on-k8s_b200/libgputopo.so" [scale_probe args]
 entries=$1; shift
 for i in 1 2 3; do
   for e in $entries; do
