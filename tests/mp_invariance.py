@@ -148,9 +148,9 @@ def shared_communicator(gt, rank, world, local):
 
 
 def different_pass_orders(gt, rank, world, local):
-    """Two contexts with a communicator each; the ranks issue their passes in different orders.  The exchanges of a
-    device run one after the other, so this can leave every rank waiting for a peer that waits for it: the waits are
-    bounded, and the call that wanted the keys fails with 'call out of order' instead of hanging."""
+    """Two contexts with a communicator each; the ranks issue their passes in different orders.  Nothing may hang:
+    every wait of the exchange is bounded, and a call that could not get the cluster's keys fails with 'call out of
+    order'."""
     ctxs = []
     for r in range(2):
         lo, hi = gt.shard_bounds(2000, rank, world)
@@ -174,7 +174,9 @@ def different_pass_orders(gt, rank, world, local):
         except gt.GtError as e:
             assert e.code == -8, e
             outcomes.append("state")
-    assert "state" in outcomes or world == 1, outcomes      # it returned: that is the point
+    # it returned: that is the point.  (With the exchange riding on the passes of its own context, mismatched orders
+    # across contexts do not even block; a rank that never shows up would end in "state" after the time limit.)
+    assert all(o in ("ok", "state") for o in outcomes), outcomes
     for a in ctxs:
         a.close()
     dist.barrier()
