@@ -117,6 +117,8 @@ struct gt_ctx {
 #endif
     // pinned host mirrors
     uint16_t *h_free = nullptr;
+    uint16_t *d_free_map = nullptr;             // device view of h_free (mapped): K0 reads a whole-shard update in place
+    bool masks_in_place = false;                // the K0 being enqueued reads the masks from the mirror, not from d_free
     uint8_t *h_ngpus = nullptr;
     uint32_t *h_ids = nullptr;
     uint16_t *h_masks = nullptr;
@@ -279,9 +281,18 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     cfg.attrs = attr;
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
-    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus, (const uint16_t *)c->d_free, d_ids, n,
+    const bool in_place = c->masks_in_place && !d_ids;
+    GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus,
+                                  (const uint16_t *)(in_place ? c->d_free_map : c->d_free), d_ids, n,
                                   c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
-                                  (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr)));
+                                  (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr),
+                                  (uint16_t *)(in_place ? c->d_free : nullptr)));
+    if (in_place) {       // the mirror may not change before this K0 has read it
+        GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
+        c->h2d_pending = true;
+        c->free_uploaded = true;
+        c->masks_in_place = false;
+    }
     c->launches++;
     return GT_OK;
 }
@@ -675,7 +686,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMemset(c->d_cost, 0, N * 256));
         GT_CUDA(c, cudaMemset(c->d_access, 0, N * 16));
         GT_CUDA(c, cudaMemset(c->d_sibling, 0, N * 32));
-        GT_CUDA(c, cudaHostAlloc(&c->h_free, N * 2, cudaHostAllocDefault));
+        GT_CUDA(c, cudaHostAlloc(&c->h_free, N * 2, cudaHostAllocMapped));
+        GT_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_free_map, c->h_free, 0));
         GT_CUDA(c, cudaHostAlloc(&c->h_ngpus, N, cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_ids, N * 4, cudaHostAllocDefault));
         GT_CUDA(c, cudaHostAlloc(&c->h_masks, N * 2, cudaHostAllocDefault));
@@ -909,10 +921,20 @@ int gt_score_all_async(gt_ctx *c)
 {
     if (!c) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
-    int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
-    if (rc != GT_OK) return rc;
+    // a whole-shard mask update needs no upload of its own: K0 reads the pinned mirror in place and refreshes the
+    // device copy as it bins (plain K0 -> K1 passes only; GT_NO_ZEROCOPY: always upload first, profiling aid)
+    static const bool no_zero_copy = getenv("GT_NO_ZEROCOPY") != nullptr;
+    const bool plain = c->n_nodes && !(c->flags & (GT_FLAG_GRAPH | GT_FLAG_MEMO_PASS));
+    if (plain && !no_zero_copy && (!c->free_uploaded || !c->dirty.empty())) {
+        c->masks_in_place = true;
+    } else {
+        int rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
+        if (rc != GT_OK) return rc;
+    }
     clear_dirty(c);
-    return enqueue_scoring(c, nullptr, c->n_nodes);
+    int rc = enqueue_scoring(c, nullptr, c->n_nodes);
+    c->masks_in_place = false;
+    return rc;
 }
 
 int gt_sync(gt_ctx *c)
@@ -1667,16 +1689,28 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
         GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
     }
     const unsigned long long *keys = out_place ? cluster_keys(c) : c->place_cur;
-    // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them
+    // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them; launched as
+    // programmatic dependents of the pass, so their launch latency is spent while K1 still runs
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(gt::kCta);
+    cfg.stream = c->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    unsigned long long *okeys = out_place ? c->d_place_map : nullptr;
+    const unsigned long long *xerr = c->d_xflags + 3;
     if (c->scores_m == m) {
         const uint32_t threads = (c->n_nodes + 15) / 16;
-        gt::k_scores_out<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-            c->d_scores, c->d_best, c->n_nodes, m, cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map),
-            keys, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+        cfg.gridDim = dim3((std::max(threads, 32u) + gt::kCta - 1) / gt::kCta);
+        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_scores_out, (const uint8_t *)c->d_scores, (const uint32_t *)c->d_best, c->n_nodes, m,
+                                      cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map), keys, okeys, xerr));
     } else {
         const uint32_t threads = (c->n_nodes + 3) / 4;
-        gt::k_sort_scores<<<(std::max(threads, 32u) + gt::kCta - 1) / gt::kCta, gt::kCta, 0, c->stream>>>(
-            c->d_best, c->n_nodes, m, cmax, c->d_scores_map, keys, out_place ? c->d_place_map : nullptr, c->d_xflags + 3);
+        cfg.gridDim = dim3((std::max(threads, 32u) + gt::kCta - 1) / gt::kCta);
+        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_sort_scores, (const uint32_t *)c->d_best, c->n_nodes, m, cmax, c->d_scores_map,
+                                      keys, okeys, xerr));
     }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
@@ -1954,7 +1988,7 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr, nullptr);
+                                                                     nullptr, nullptr, nullptr);
     gt::ScoreParams prm = {};
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;

@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               const uint32_t *__restrict__ ids, uint32_t n, uint32_t cap,
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
-                                              unsigned long long *__restrict__ place, uint8_t *__restrict__ scores)
+                                              unsigned long long *__restrict__ place, uint8_t *__restrict__ scores,
+                                              uint16_t *__restrict__ free_copy)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
@@ -262,7 +263,11 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
         node = ids ? ids[i] : i;
         uint32_t ng = n_gpus[node];
         ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-        f = (uint32_t)free_mask[node] & ((1u << ng) - 1u);
+        const uint32_t raw = free_mask[node];
+        // free_mask may be the caller's pinned host mirror read in place (whole-shard update): the device copy that
+        // later passes over single nodes read is refreshed on the way, no separate upload
+        if (free_copy) free_copy[node] = (uint16_t)raw;
+        f = raw & ((1u << ng) - 1u);
         p = __popc(f);
         slot = atomicAdd(&s_cnt[p], 1u);
         if (p >= kSplitP) {   // several warp units of K1 meet in this row through atomicMin
@@ -1329,6 +1334,7 @@ __global__ void __launch_bounds__(kCta) k_sort_scores(const uint32_t *__restrict
                                                       const unsigned long long *__restrict__ xerr)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // launched while the pass still runs: wait for its rows
     if (out_place && t < 16) out_place[t] = place[t];
     if (out_place && t == 16) out_place[16] = *xerr;     // non-zero: a min-exchange gave up on a peer
     const uint32_t i0 = t * 4;
@@ -1360,6 +1366,7 @@ __global__ void __launch_bounds__(kCta) k_scores_out(const uint8_t *__restrict__
                                                      const unsigned long long *__restrict__ xerr)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // launched while the pass still runs: wait for its rows
     if (out_place && t < 16) out_place[t] = place[t];
     if (out_place && t == 16) out_place[16] = *xerr;     // non-zero: a min-exchange gave up on a peer
     const uint32_t i0 = t * 16;
