@@ -103,7 +103,18 @@ constexpr int kCtlTicket = 17, kCtlDone = 18;
 // warp's first unit costs more than the whole decode.
 __host__ __device__ constexpr int bin_order_host(int i)
 {
+#ifndef GT_BIN_ORDER
+#define GT_BIN_ORDER 0
+#endif
+#if GT_BIN_ORDER == 0
     constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 1   // longest measured unit first
+    constexpr int order[kBins] = {12, 11, 13, 16, 15, 14, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 2   // many-lanes-per-node units by descending p, then the one-lane-per-node ones
+    constexpr int order[kBins] = {16, 15, 14, 13, 12, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2, 1, 0};
+#else                     // split nodes first (their units are the only ones that cannot start late), then by length
+    constexpr int order[kBins] = {16, 15, 14, 12, 11, 13, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
+#endif
     return order[i];
 }
 __host__ __device__ constexpr unsigned long long bin_order_pack(int from, int to)
@@ -618,7 +629,12 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
     const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
     if (prm.xw.world && blockIdx.x == 0 && warp == kScoreCta / 32 - 1) exchange_step(prm.xw, lane);   // multi-GPU, see there
-    uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
+#ifndef GT_FIRST_UNIT_RR
+#define GT_FIRST_UNIT_RR 0
+#endif
+    // first unit: GT_FIRST_UNIT_RR deals the first n_warps units round-robin over the CTAs, so that the warps of one SM
+    // start on units of different kinds (their memory and ALU phases then interleave instead of coinciding)
+    uint32_t u = GT_FIRST_UNIT_RR ? warp * gridDim.x + blockIdx.x : blockIdx.x * (kScoreCta / 32) + warp;
     int i = 0;
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;

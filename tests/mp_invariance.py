@@ -14,6 +14,11 @@ import _pkg
 import oracle_lib
 
 
+def stage(rank, what):
+    if rank == 0:
+        print("mp_invariance: " + what, flush=True)
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -38,14 +43,17 @@ def main():
                 assert (got == want).all(), (what, got, want)
             return got
 
+        stage(rank, "communicator up, mode %d" % a.comm_mode())
         for _ in range(3):
             a.score_all(fetch=False)
             got = check(ffr, "full pass")
+        stage(rank, "full passes ok")
         # many passes back to back without a consumer in between: both key buffers are reused again and again and
         # each exchange must have let go of its buffer before the pass two later resets it
         for _ in range(40):
             a.score_all_async()
         got = check(ffr, "40 passes back to back")
+        stage(rank, "40 passes back to back ok")
         # the free masks change between passes (every rank draws the whole cluster's masks from the same seed)
         rng = np.random.RandomState(7)
         for it in range(4):
@@ -63,7 +71,9 @@ def main():
         cur = gcur.cpu().numpy().astype(np.uint16)
         a.update_free(cur[lo + ids], node_ids=ids)
         a.score_dirty()
+        stage(rank, "new masks ok")
         got = check(cur, "dirty pass")
+        stage(rank, "dirty pass ok")
         for _ in range(5):
             a.score_all_async()
         got = check(cur, "full passes after a dirty pass")
@@ -78,10 +88,14 @@ def main():
     dist.broadcast(ref, 0)
     assert bool((t == ref).all())
     dist.barrier()
+    stage(rank, "single context ok")
     schedule_sharded(gt, rank, world, local)
+    stage(rank, "sharded gt_schedule ok")
     shared_communicator(gt, rank, world, local)
+    stage(rank, "shared communicator ok")
     if not os.environ.get("GT_NO_P2P"):
         different_pass_orders(gt, rank, world, local)
+        stage(rank, "different pass orders ok")
     if rank == 0:
         print("mp_invariance ok: world=%d exchange=%s" % (world, "nccl" if os.environ.get("GT_NO_P2P") else "peer memory"))
     dist.destroy_process_group()

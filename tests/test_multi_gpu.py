@@ -26,6 +26,6 @@ def test_min_exchange_matches_oracle(exchange):
         env["GT_NO_P2P"] = "1"
     else:
         env.pop("GT_NO_P2P", None)
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "mp_invariance ok" in r.stdout and "exchange=%s" % exchange in r.stdout
