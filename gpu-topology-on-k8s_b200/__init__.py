@@ -454,8 +454,8 @@ class Allocator:
 
 
 def time_pass_rotated(allocators, iters=64):
-    """(K0, K1, K0+K1) microseconds per launch, each kernel timed alone while the contexts take turns (cold L2 once
-    their tables exceed it)."""
+    """(pass - K1, K1, pass) microseconds: passes back to back while the contexts take turns (cold L2 once their tables
+    exceed it), K1 timed in place by its own global-timer stamps."""
     arr = (C.c_void_p * len(allocators))(*[a._h.value for a in allocators])
     out = (C.c_float * 3)()
     rc = _lib().gt_time_pass_rotated(arr, len(allocators), iters, out)

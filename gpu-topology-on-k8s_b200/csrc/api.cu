@@ -118,6 +118,7 @@ struct gt_ctx {
     // pinned host mirrors
     uint16_t *h_free = nullptr;
     uint16_t *d_free_map = nullptr;             // device view of h_free (mapped): K0 reads a whole-shard update in place
+    unsigned long long *ktime_next = nullptr;   // measurement: where the next K1 leaves its time stamps
     bool masks_in_place = false;                // the K0 being enqueued reads the masks from the mirror, not from d_free
     uint8_t *h_ngpus = nullptr;
     uint32_t *h_ids = nullptr;
@@ -327,6 +328,7 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     gt::ScoreParams prm = score_params(c, fold, keep_bins);
+    prm.ktime = c->ktime_next;
     if (xw) prm.xw = *xw;     // multi-GPU: one warp of this K1 does the exchange work of the two passes before it
     // GT_PIPE=1: the producer / consumer form of K1 for full passes -- same results (it passes every parity test), but
     // its one producer warp per CTA cannot describe units as fast as the consumers finish them, so it measures 2-3x
@@ -1097,9 +1099,10 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     return GT_OK;
 }
 
-// K0 and K1 timed one by one while the contexts take turns: with more replicas than fit the L2 every launch finds
-// its tables in DRAM, as the launches of a rotated scoring loop do.  Events sit between the kernels, so each runs
-// alone (no programmatic overlap with its neighbour): out_us = {K0, K1, K0 + K1} averages per launch.
+// Full passes back to back (programmatic launches intact, as in a scoring loop) while the contexts take turns: with
+// more replicas than fit the L2 every launch finds its tables in DRAM.  K1 stamps the global timer when its first CTA
+// gets past the dependency wait and when its last CTA finishes: out_us = {pass - K1 (K0 and the two hand-overs), K1
+// in place, pass}, averages over `iters` passes.
 int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float out_us[3])
 {
     if (!ctxs || !n_ctx || !iters || !out_us) return GT_ERR_INVALID;
@@ -1109,9 +1112,7 @@ int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float ou
         if (!ctxs[i] || ctxs[i]->device != c0->device || ctxs[i]->stream != c0->stream || !ctxs[i]->n_nodes)
             return fail(c0, GT_ERR_INVALID, "gt_time_pass_rotated: contexts must share device and stream%s");
     GT_CUDA(c0, cudaSetDevice(c0->device));
-    iters = std::min<uint32_t>(iters, 256);
-    std::vector<cudaEvent_t> ev((size_t)iters * 3);
-    for (auto &e : ev) GT_CUDA(c0, cudaEventCreate(&e));
+    iters = std::min<uint32_t>(iters, 4096);
     int rc = GT_OK;
     for (uint32_t i = 0; i < n_ctx && rc == GT_OK; i++) {
         gt_ctx *c = ctxs[i];
@@ -1121,31 +1122,32 @@ int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float ou
         rc = flush_free(c, !c->free_uploaded || !c->dirty.empty());
         clear_dirty(c);
     }
+    if (rc != GT_OK) return rc;
+    struct Buf { unsigned long long *p = nullptr; ~Buf() { cudaFree(p); } } stamps;
+    GT_CUDA(c0, cudaMalloc(&stamps.p, (size_t)iters * 2 * sizeof(unsigned long long)));
+    GT_CUDA(c0, cudaMemsetAsync(stamps.p, 0, (size_t)iters * 2 * sizeof(unsigned long long), c0->stream));
     for (uint32_t it = 0; it < iters + n_ctx && rc == GT_OK; it++) {   // first round over the contexts: warm-up
         gt_ctx *c = ctxs[it % n_ctx];
         void *saved = c->comm;
         c->comm = nullptr;   // a local measurement: other ranks are not in this call
-        const bool timed = it >= n_ctx;
-        cudaEvent_t *e = timed ? &ev[(size_t)(it - n_ctx) * 3] : nullptr;
-        if (timed) cudaEventRecord(e[0], c->stream);
         rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
-        if (timed) cudaEventRecord(e[1], c->stream);
+        c->ktime_next = it >= n_ctx ? stamps.p + 2 * (size_t)(it - n_ctx) : nullptr;
         if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, 0));
-        if (timed) cudaEventRecord(e[2], c->stream);
+        c->ktime_next = nullptr;
         c->comm = saved;
         c->place_valid = false;
     }
     GT_CUDA(c0, cudaStreamSynchronize(c0->stream));
-    double sum[3] = {0, 0, 0};
-    for (uint32_t it = 0; it < iters && rc == GT_OK; it++) {
-        float a = 0, b = 0;
-        cudaEventElapsedTime(&a, ev[(size_t)it * 3], ev[(size_t)it * 3 + 1]);
-        cudaEventElapsedTime(&b, ev[(size_t)it * 3 + 1], ev[(size_t)it * 3 + 2]);
-        sum[0] += a; sum[1] += b; sum[2] += a + b;
-    }
-    for (auto &e : ev) cudaEventDestroy(e);
-    for (int q = 0; q < 3; q++) out_us[q] = (float)(sum[q] * 1e3 / iters);
-    return rc;
+    if (rc != GT_OK) return rc;
+    std::vector<unsigned long long> h((size_t)iters * 2);
+    GT_CUDA(c0, cudaMemcpy(h.data(), stamps.p, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    double k1 = 0;
+    for (uint32_t it = 0; it < iters; it++) k1 += (double)(h[2 * it + 1] - h[2 * it]);
+    const double pass = iters > 1 ? (double)(h[2 * (iters - 1) + 1] - h[1]) / (iters - 1) : (double)(h[1] - h[0]);
+    out_us[1] = (float)(k1 / iters * 1e-3);
+    out_us[2] = (float)(pass * 1e-3);
+    out_us[0] = out_us[2] - out_us[1];
+    return GT_OK;
 }
 
 // This rank's own 16 placement keys, recomputed from its best table (K2) without any exchange: what a checker

@@ -66,6 +66,7 @@ struct ScoreParams {
     uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
+    unsigned long long *ktime;      // measurement: [0] globaltimer when CTA 0 got past the dependency wait, [1] when the last CTA finished (null = off)
     XWork xw;                       // multi-GPU: exchange work of the two passes before this one, done by one warp of K1
     uint8_t *scores;                // `sort` verb inside the pass: HostPriority score 0..10 of every node for request size
     uint32_t score_k, score_den;    // score_k (1..16; 0 = off), den = cmax * C(score_k, 2); see score_byte()
@@ -592,6 +593,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 #endif
     if (tid < 16) s_place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible (no-op without PDL)
+    if (prm.ktime && blockIdx.x == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prm.ktime[0]));
     GT_TR(2);
     if (GT_K1_TRIGGER == 1) asm volatile("griddepcontrol.launch_dependents;");
 #ifdef GT_TRACE
@@ -733,6 +735,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
             prm.ctl[kCtlDone] = 0u;
+            if (prm.ktime) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prm.ktime[1]));
         }
     }
 }
@@ -868,6 +871,7 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
     }
     if (tid < 16) sh.place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible
+    if (prm.ktime && blockIdx.x == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prm.ktime[0]));
     if (warp == 0) {
         uint32_t units = 0, cnt = 0;
         int p = 0;
@@ -1071,6 +1075,7 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
                 for (int q = 0; q < kBins; q++) prm.ctl[q] = 0u;
             prm.ctl[kCtlTicket] = 0u;
             prm.ctl[kCtlDone] = 0u;
+            if (prm.ktime) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prm.ktime[1]));
         }
     }
 }

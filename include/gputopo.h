@@ -260,8 +260,9 @@ int gt_count_subsets(gt_ctx *ctx, uint64_t *out_subsets, uint64_t *out_pair_adds
 /* time `iters` back-to-back launches of one kernel ("step", "step_nograph", "bin", "score", "argmin", "int32_peak") with
  * CUDA events on the context's stream; out_ms = average per launch */
 int gt_time_kernel(gt_ctx *ctx, const char *which, uint32_t iters, float *out_ms);
-/* K0 and K1 timed launch by launch (CUDA events between the kernels) while n_ctx contexts on one device and stream take
- * turns, so that every launch finds its tables in DRAM once the replicas exceed the L2: out_us = {K0, K1, K0+K1} */
+/* full passes back to back while n_ctx contexts on one device and stream take turns, so that every launch finds its
+ * tables in DRAM once the replicas exceed the L2; K1 stamps the global timer itself (first CTA past the dependency wait,
+ * last CTA done), nothing sits between the launches: out_us = {pass - K1, K1 in place, pass} */
 int gt_time_pass_rotated(gt_ctx **ctxs, uint32_t n_ctx, uint32_t iters, float out_us[3]);
 /* this rank's own 16 placement keys recomputed from its best table, no exchange: the min over ranks of these is what
  * gt_best_node must return on every rank (checked by bench.py and the multi-GPU tests) */
