@@ -104,18 +104,7 @@ constexpr int kCtlTicket = 17, kCtlDone = 18;
 // warp's first unit costs more than the whole decode.
 __host__ __device__ constexpr int bin_order_host(int i)
 {
-#ifndef GT_BIN_ORDER
-#define GT_BIN_ORDER 0
-#endif
-#if GT_BIN_ORDER == 0
     constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
-#elif GT_BIN_ORDER == 1   // longest measured unit first
-    constexpr int order[kBins] = {12, 11, 13, 16, 15, 14, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
-#elif GT_BIN_ORDER == 2   // many-lanes-per-node units by descending p, then the one-lane-per-node ones
-    constexpr int order[kBins] = {16, 15, 14, 13, 12, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2, 1, 0};
-#else                     // split nodes first (their units are the only ones that cannot start late), then by length
-    constexpr int order[kBins] = {16, 15, 14, 12, 11, 13, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
-#endif
     return order[i];
 }
 __host__ __device__ constexpr unsigned long long bin_order_pack(int from, int to)
@@ -304,6 +293,17 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     if (tid == 0) GT_KT_MAX(1, gt_now());
 #endif
     asm volatile("griddepcontrol.launch_dependents;");
+}
+
+// 16 bytes global -> shared without a register stop-over (LDGSTS).  Staging loops issue all their copies first and
+// wait once: one DRAM round trip per unit, however many tiles it has.
+__device__ __forceinline__ void copy16_async(void *dst, const void *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void copies_landed()
+{
+    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 // ---------------------------------------------------------------- the unrolled subset tree
@@ -534,14 +534,18 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     const uint32_t f = __ldg(flist + first + (active ? slot : 0u));
     if (f == 0x12345u) GT_TR(99);
     GT_TR(10);   // list entries arrived
-    // stage tiles: 16 lanes x 16 B per tile, two tiles per pass
-    for (uint32_t t = lane >> 4; t < live; t += 2) {
-        const uint32_t nd = __ldg(list + first + t);
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(prm.cost + (size_t)nd * 256) + (lane & 15u));
-        *reinterpret_cast<uint4 *>(ws.raw + t * kTileStride + (lane & 15u) * 16) = v;
+    // stage tiles: 16 lanes x 16 B per tile, two tiles per copy instruction; all copies are issued before any is
+    // waited for (a load -> store loop paid one memory round trip per iteration, eight of them for a p = 9 unit)
+#pragma unroll
+    for (int it = 0; it < kTilesPerWarp / 2; it++) {
+        const uint32_t t = 2u * (uint32_t)it + (lane >> 4);
+        const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, (int)((t << (hb <= 5 ? hb : 0)) & 31u));   // slot t's first lane
+        if (t < live)
+            copy16_async(ws.raw + t * kTileStride + (lane & 15u) * 16, prm.cost + (size_t)nd * 256 + (lane & 15u) * 16);
     }
     for (uint32_t s2 = 0; s2 < live; s2++)
         if (lane < (uint32_t)kBins) ws.best[s2][lane] = kInf;
+    copies_landed();
     __syncwarp();
     GT_TR(11);   // tiles staged
     if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
@@ -631,12 +635,9 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
     const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
     if (prm.xw.world && blockIdx.x == 0 && warp == kScoreCta / 32 - 1) exchange_step(prm.xw, lane);   // multi-GPU, see there
-#ifndef GT_FIRST_UNIT_RR
-#define GT_FIRST_UNIT_RR 0
-#endif
-    // first unit: GT_FIRST_UNIT_RR deals the first n_warps units round-robin over the CTAs, so that the warps of one SM
-    // start on units of different kinds (their memory and ALU phases then interleave instead of coinciding)
-    uint32_t u = GT_FIRST_UNIT_RR ? warp * gridDim.x + blockIdx.x : blockIdx.x * (kScoreCta / 32) + warp;
+    // (dealing the first units round-robin over the CTAs, or handing the longest units out first, measured slower
+    // both with warm and with cold L2: profiles/r2_cold_ab_orders_staging.txt)
+    uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
     int i = 0;
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
@@ -676,15 +677,15 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             {
                 const uint32_t row = lane & 15u;
                 __syncwarp();
-#pragma unroll 8
-                for (int t = 0; t < 16; t++) {
+#pragma unroll
+                for (int t = 0; t < 16; t++) {       // asynchronous copies, all in flight together: one round trip
                     const int s2 = 2 * t + (int)(lane >> 4);
                     const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, s2);
                     const uint32_t ff = __shfl_sync(0xFFFFFFFFu, f, s2);     // 0 for slots beyond the bin's end
                     if ((ff >> row) & 1u)
-                        *reinterpret_cast<uint4 *>(ws.raw + s2 * kTileStride + row * 16) =
-                            __ldg(reinterpret_cast<const uint4 *>(prm.cost + (size_t)nd * 256) + row);
+                        copy16_async(ws.raw + s2 * kTileStride + row * 16, prm.cost + (size_t)nd * 256 + row * 16);
                 }
+                copies_landed();
                 __syncwarp();
             }
             if (ok) {
@@ -817,14 +818,9 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t pari
         }
     }
 }
-// 16 bytes global -> shared without a register stop-over (LDGSTS), and the arrival that fires once all of this
-// thread's earlier copies have landed.  (One bulk copy per node -- cp.async.bulk, 64-256 bytes each -- was measured
-// first: the copy engine delivered about 2 bytes per ns per SM on such small scattered pieces, 3x slower than the
-// kernel it was meant to feed: profiles/r2_ab_pipe_bulkcopy_v1.txt.)
-__device__ __forceinline__ void copy16_async(void *dst, const void *src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
+// the arrival that fires once all of this thread's earlier asynchronous copies have landed.  (One bulk copy per node --
+// cp.async.bulk, 64-256 bytes each -- was measured first: the copy engine delivered about 2 bytes per ns per SM on
+// such small scattered pieces, 3x slower than the kernel it was meant to feed: profiles/r2_ab_pipe_bulkcopy_v1.txt.)
 __device__ __forceinline__ void mbar_arrive_after_copies(unsigned long long *bar)
 {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
