@@ -39,7 +39,8 @@ constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the r
 constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
 constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 16: shifts banks between tiles)
 #ifndef GT_SMALL_SMEM
-#define GT_SMALL_SMEM 1   // one-lane-per-node units read their pair costs from tiles the warp staged in shared memory
+#define GT_SMALL_SMEM 0   // 1: one-lane-per-node units read their pair costs from tiles the warp staged in shared memory
+                          // (0.6 us per pass faster with warm L2, 0.4 us slower with cold L2: profiles/r2_cold_ab_async_staging.txt)
 #endif
 constexpr int kStageBytes = (GT_SMALL_SMEM ? 32 : kTilesPerWarp) * kTileStride;   // staging buffer of a warp: 16 full tiles (32 for small units)
 constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
@@ -104,7 +105,14 @@ constexpr int kCtlTicket = 17, kCtlDone = 18;
 // warp's first unit costs more than the whole decode.
 __host__ __device__ constexpr int bin_order_host(int i)
 {
+#ifndef GT_BIN_ORDER
+#define GT_BIN_ORDER 0
+#endif
+#if GT_BIN_ORDER == 0
     constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+#else                     // longest measured unit first
+    constexpr int order[kBins] = {12, 11, 13, 16, 15, 14, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
+#endif
     return order[i];
 }
 __host__ __device__ constexpr unsigned long long bin_order_pack(int from, int to)
@@ -504,10 +512,23 @@ struct WarpScratch {
     uint32_t best[kTilesPerWarp][kBins];
 };
 
+#ifndef GT_LATE_TICKET
+#define GT_LATE_TICKET 0   // 1: ask for the next unit after the tree instead of at the start of the current unit
+#endif
+// next unit number from the global ticket.  ptxas turns an atomic add on a provably warp-uniform address (even from
+// inline PTX, even atom.inc) into a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once:
+// the address therefore carries a run-time zero times the lane index.
+__device__ __forceinline__ uint32_t take_ticket(const ScoreParams &prm, uint32_t lane)
+{
+    uint32_t next;
+    asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket + prm.zero * lane) : "memory");
+    return next;
+}
+
 // hb = p - 8 bits of H.  hb <= 5: a warp holds 32 >> hb nodes.  hb > 5: a node spans 2^(hb-5) warp units
 // whose minima meet in global memory (rows preset to kInf by k_bin).
 __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScratch &ws, WarpBest &wb,
-                                               int p, uint32_t lu, uint32_t cnt, uint32_t lane
+                                               int p, uint32_t lu, uint32_t cnt, uint32_t lane, uint32_t &next
 #ifdef GT_TRACE
                                                , unsigned long long *tr, int &tr_n
 #endif
@@ -550,6 +571,7 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     GT_TR(11);   // tiles staged
     if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
     __syncwarp();
+    if (GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);   // the reply arrives during the write-out
     GT_TR(12);   // set-up + tree + atomics done
     if (hb <= 5) {
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
@@ -643,8 +665,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
     while (u < total) {
         uint32_t next = 0;
-        if (lane == 0)
-            asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket + prm.zero * tid) : "memory");
+        if (!GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);
         // `next` is not touched again before the end of this unit: the reply has a whole unit to arrive
         while (u >= s_end[i]) i++;            // units only grow: continue from the previous bin
         const int p = bin_order(i);
@@ -653,9 +674,9 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         GT_TR(32 + p);   // unit start
         if (p > 8) {
 #ifdef GT_TRACE
-            score_big_warp(prm, ws, wb, p, lu, cnt, lane, tr, tr_n);
+            score_big_warp(prm, ws, wb, p, lu, cnt, lane, next, tr, tr_n);
 #else
-            score_big_warp(prm, ws, wb, p, lu, cnt, lane);
+            score_big_warp(prm, ws, wb, p, lu, cnt, lane, next);
 #endif
         } else {
             const uint32_t idx = lu * 32u + lane;
@@ -702,6 +723,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 o[3] = make_uint4(kInf, kInf, kInf, kInf);
                 if (prm.score_k) prm.scores[node] = (uint8_t)score_byte(pick_row(out, prm.score_k), prm.score_den);
             }
+            if (GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);   // the reply arrives during the fold
             if (prm.fold_place) {
                 fold_small_warp4<0>(wb, out, node, lane);
                 if (p > 4) fold_small_warp4<4>(wb, out, node, lane);
