@@ -39,8 +39,8 @@ constexpr int kScoreMinCtas = GT_SCORE_MIN_CTAS;   // resident CTAs per SM the r
 constexpr int kTilesPerWarp = 16;    // nodes per warp unit at p = 9 (2 lanes per node)
 constexpr int kTileStride = 272;     // bytes per staged 16x16 cost tile (256 + 16: shifts banks between tiles)
 #ifndef GT_SMALL_SMEM
-#define GT_SMALL_SMEM 0   // 1: one-lane-per-node units read their pair costs from tiles the warp staged in shared memory
-                          // (0.6 us per pass faster with warm L2, 0.4 us slower with cold L2: profiles/r2_cold_ab_async_staging.txt)
+#define GT_SMALL_SMEM 1   // one-lane-per-node units read their pair costs from tiles the warp staged in shared memory
+                          // (0: byte gathers from global memory; A/B in profiles/r2_cold_ab_*.txt)
 #endif
 constexpr int kStageBytes = (GT_SMALL_SMEM ? 32 : kTilesPerWarp) * kTileStride;   // staging buffer of a warp: 16 full tiles (32 for small units)
 constexpr int kSplitP = 14;          // nodes with p >= kSplitP span several warp units
@@ -303,6 +303,66 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     asm volatile("griddepcontrol.launch_dependents;");
 }
 
+// K0 with one small CTA per SM (experiment, GT_K0_PERSIST=1): 128 threads and <= 32 registers, so that a CTA fits beside
+// K1's five resident CTAs on every SM.  Launched as a programmatic dependent it is then already resident, waiting at
+// griddepcontrol.wait, when K1 finishes -- the hand-over no longer pays for scheduling a fresh grid.  Each CTA bins a
+// contiguous slice of <= 1024 nodes held in registers between the counting and the scattering round: one global atomic
+// per bin and CTA.
+constexpr int kBinPersistCta = 128, kBinPersistRounds = 8;
+__global__ void __launch_bounds__(kBinPersistCta) k_bin_persist(const uint8_t *__restrict__ n_gpus,
+                                                                 const uint16_t *__restrict__ free_mask, uint32_t n, uint32_t cap,
+                                                                 uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
+                                                                 uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
+                                                                 unsigned long long *__restrict__ place,
+                                                                 uint8_t *__restrict__ scores, uint16_t *__restrict__ free_copy,
+                                                                 uint32_t trigger_top)
+{
+    __shared__ uint32_t s_cnt[kBins], s_base[kBins];
+    const uint32_t tid = threadIdx.x;
+    if (tid < kBins) s_cnt[tid] = 0;
+    if (trigger_top) asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
+    __syncthreads();
+    const uint32_t per = (n + gridDim.x - 1) / gridDim.x;
+    const uint32_t lo = blockIdx.x * per, hi = min(n, lo + per);
+    uint32_t fp[kBinPersistRounds], slot[kBinPersistRounds];    // free mask | p << 16 (p = 31: no node)
+#pragma unroll
+    for (int r = 0; r < kBinPersistRounds; r++) {
+        const uint32_t node = lo + (uint32_t)r * kBinPersistCta + tid;
+        fp[r] = 31u << 16; slot[r] = 0;
+        if (node < hi) {
+            uint32_t ng = n_gpus[node];
+            ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
+            const uint32_t raw = free_mask[node];
+            if (free_copy) free_copy[node] = (uint16_t)raw;
+            const uint32_t f = raw & ((1u << ng) - 1u);
+            const uint32_t p = (uint32_t)__popc(f);
+            fp[r] = f | (p << 16);
+            slot[r] = atomicAdd(&s_cnt[p], 1u);
+            if (p >= (uint32_t)kSplitP) {
+                uint4 *o = reinterpret_cast<uint4 *>(best + (size_t)node * 16);
+                const uint4 inf = make_uint4(kInf, kInf, kInf, kInf);
+                o[0] = inf; o[1] = inf; o[2] = inf; o[3] = inf;
+                if (scores) scores[node] = (uint8_t)kScorePending;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&ctl[tid], s_cnt[tid]);
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kBinPersistRounds; r++) {
+        const uint32_t p = fp[r] >> 16;
+        if (p != 31u) {
+            const size_t at = (size_t)p * cap + s_base[p] + slot[r];
+            bin_list[at] = lo + (uint32_t)r * kBinPersistCta + tid;
+            bin_free[at] = (uint16_t)fp[r];
+        }
+    }
+    if (!trigger_top) asm volatile("griddepcontrol.launch_dependents;");
+}
+
 // 16 bytes global -> shared without a register stop-over (LDGSTS).  Staging loops issue all their copies first and
 // wait once: one DRAM round trip per unit, however many tiles it has.
 __device__ __forceinline__ void copy16_async(void *dst, const void *src)
@@ -513,7 +573,9 @@ struct WarpScratch {
 };
 
 #ifndef GT_LATE_TICKET
-#define GT_LATE_TICKET 0   // 1: ask for the next unit after the tree instead of at the start of the current unit
+#define GT_LATE_TICKET 1   // ask for the next unit after the tree instead of at the start of the current unit: a ticket taken
+                           // at the start reserves a unit that then waits behind a long one while other warps run dry
+                           // (0.5 us per pass at 100 000 nodes, profiles/r2_cold_ab_late_ticket.txt)
 #endif
 // next unit number from the global ticket.  ptxas turns an atomic add on a provably warp-uniform address (even from
 // inline PTX, even atom.inc) into a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once:
