@@ -283,18 +283,6 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     const bool in_place = c->masks_in_place && !d_ids;
-    static const bool persist = getenv("GT_K0_PERSIST") != nullptr, trig_top = getenv("GT_K0_TRIGGER_TOP") != nullptr;   // experiment
-    if (persist && !d_ids && n) {
-        const uint32_t per_cta = gt::kBinPersistCta * gt::kBinPersistRounds;
-        cfg.gridDim = dim3(std::max<uint32_t>(std::min<uint32_t>((uint32_t)c->num_sms, (n + gt::kBinPersistCta - 1) / gt::kBinPersistCta),
-                                              (n + per_cta - 1) / per_cta));
-        cfg.blockDim = dim3(gt::kBinPersistCta);
-        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin_persist, (const uint8_t *)c->d_ngpus,
-                                      (const uint16_t *)(in_place ? c->d_free_map : c->d_free), n, c->cap, c->d_bin_cnt,
-                                      c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
-                                      (uint8_t *)((c->want_score_m && preset_place) ? c->d_scores : nullptr),
-                                      (uint16_t *)(in_place ? c->d_free : nullptr), (uint32_t)(trig_top ? 1 : 0)));
-    } else
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus,
                                   (const uint16_t *)(in_place ? c->d_free_map : c->d_free), d_ids, n,
                                   c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place,

@@ -296,71 +296,13 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     }
     // programmatic dependent launch: from here on K1's CTAs may be scheduled while this grid drains; K1 waits
     // (griddepcontrol.wait) for the whole grid before it reads the bins.  Triggering at the top of K0 instead
-    // was measured 3-6 us slower per pass: the waiting K1 CTAs crowd K0 off the SMs.
+    // was measured 3-6 us slower per pass: the waiting K1 CTAs crowd K0 off the SMs.  (A K0 of one 128-thread,
+    // 32-register CTA per SM, small enough to sit resident beside K1's CTAs and start the moment K1 ends, was
+    // measured too: 20.2 instead of 17.8 us per pass, profiles/r2_cold_ab_k0_persist_trigger.txt.)
 #ifdef GT_TRACE
     if (tid == 0) GT_KT_MAX(1, gt_now());
 #endif
     asm volatile("griddepcontrol.launch_dependents;");
-}
-
-// K0 with one small CTA per SM (experiment, GT_K0_PERSIST=1): 128 threads and <= 32 registers, so that a CTA fits beside
-// K1's five resident CTAs on every SM.  Launched as a programmatic dependent it is then already resident, waiting at
-// griddepcontrol.wait, when K1 finishes -- the hand-over no longer pays for scheduling a fresh grid.  Each CTA bins a
-// contiguous slice of <= 1024 nodes held in registers between the counting and the scattering round: one global atomic
-// per bin and CTA.
-constexpr int kBinPersistCta = 128, kBinPersistRounds = 8;
-__global__ void __launch_bounds__(kBinPersistCta) k_bin_persist(const uint8_t *__restrict__ n_gpus,
-                                                                 const uint16_t *__restrict__ free_mask, uint32_t n, uint32_t cap,
-                                                                 uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
-                                                                 uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
-                                                                 unsigned long long *__restrict__ place,
-                                                                 uint8_t *__restrict__ scores, uint16_t *__restrict__ free_copy,
-                                                                 uint32_t trigger_top)
-{
-    __shared__ uint32_t s_cnt[kBins], s_base[kBins];
-    const uint32_t tid = threadIdx.x;
-    if (tid < kBins) s_cnt[tid] = 0;
-    if (trigger_top) asm volatile("griddepcontrol.launch_dependents;");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
-    __syncthreads();
-    const uint32_t per = (n + gridDim.x - 1) / gridDim.x;
-    const uint32_t lo = blockIdx.x * per, hi = min(n, lo + per);
-    uint32_t fp[kBinPersistRounds], slot[kBinPersistRounds];    // free mask | p << 16 (p = 31: no node)
-#pragma unroll
-    for (int r = 0; r < kBinPersistRounds; r++) {
-        const uint32_t node = lo + (uint32_t)r * kBinPersistCta + tid;
-        fp[r] = 31u << 16; slot[r] = 0;
-        if (node < hi) {
-            uint32_t ng = n_gpus[node];
-            ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-            const uint32_t raw = free_mask[node];
-            if (free_copy) free_copy[node] = (uint16_t)raw;
-            const uint32_t f = raw & ((1u << ng) - 1u);
-            const uint32_t p = (uint32_t)__popc(f);
-            fp[r] = f | (p << 16);
-            slot[r] = atomicAdd(&s_cnt[p], 1u);
-            if (p >= (uint32_t)kSplitP) {
-                uint4 *o = reinterpret_cast<uint4 *>(best + (size_t)node * 16);
-                const uint4 inf = make_uint4(kInf, kInf, kInf, kInf);
-                o[0] = inf; o[1] = inf; o[2] = inf; o[3] = inf;
-                if (scores) scores[node] = (uint8_t)kScorePending;
-            }
-        }
-    }
-    __syncthreads();
-    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&ctl[tid], s_cnt[tid]);
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < kBinPersistRounds; r++) {
-        const uint32_t p = fp[r] >> 16;
-        if (p != 31u) {
-            const size_t at = (size_t)p * cap + s_base[p] + slot[r];
-            bin_list[at] = lo + (uint32_t)r * kBinPersistCta + tid;
-            bin_free[at] = (uint16_t)fp[r];
-        }
-    }
-    if (!trigger_top) asm volatile("griddepcontrol.launch_dependents;");
 }
 
 // 16 bytes global -> shared without a register stop-over (LDGSTS).  Staging loops issue all their copies first and
