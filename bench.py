@@ -396,6 +396,10 @@ def main():
     # ---- roofline of the dominant kernel (K1): CUDA events around each launch, replicas taking turns so
     # that every launch reads its tables from DRAM like the launches of the `value` loop do
     roofline, kernels, peak_adds = None, {}, None
+    if world > 1:       # what follows is rank-local: no context may still owe its peers an exchange
+        for c in ctxs:
+            c.best_node(ks)
+        barrier()
     if rank == 0:
         c = ctxs[0]
         rest_us, k1_us, pass_us = gt.time_pass_rotated(ctxs, 256)

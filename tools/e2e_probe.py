@@ -2,28 +2,61 @@
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import _pkg, torch
+import _pkg
 gt = _pkg.load_package()
 N = 100000
-lv, ng, fr, _ = gt.synth_cluster(4, 0x5EED0004, 0, N)
-pin = torch.empty(N, dtype=torch.int16).pin_memory(); fnp = pin.numpy().view(np.uint16); fnp[:] = fr
-sc = torch.empty(N, dtype=torch.uint8).pin_memory().numpy()
-pl = np.zeros(16, np.uint64)
-with gt.Allocator(N) as a:
+R = 8
+ctxs = []
+for r in range(R):                       # rotated replicas: cold L2 as in bench.py
+    lv, ng, fr, _ = gt.synth_cluster(4, 0x5EED0004 + r, 0, N)
+    a = gt.Allocator(N)
     a.load_nodes(lv, ng, fr)
-    for _ in range(20):
-        a.update_free(fnp); a.ext_sort_into(2, sc, pl)
-    T = 500
+    a.host_free()[:N] = fr
+    ctxs.append(a)
+pl = np.zeros(16, np.uint64)
+T = 400
+
+
+def timed(f):
+    for i in range(20):
+        f(i)
     t0 = time.perf_counter()
-    for _ in range(T): a.update_free(fnp)
-    t1 = time.perf_counter()
-    for _ in range(T): a.update_free(fnp); a.ext_sort_into(2, sc, pl)
-    t2 = time.perf_counter()
-    for _ in range(T): a.ext_sort_into(2, sc, pl)       # nothing dirty: sort kernel + copies only
-    t3 = time.perf_counter()
-    for _ in range(T): a.score_all_async(); a.sync()
-    t4 = time.perf_counter()
-    print("update_free alone      %.1f us" % ((t1 - t0) / T * 1e6))
-    print("update_free + ext_sort %.1f us" % ((t2 - t1) / T * 1e6))
-    print("ext_sort, nothing dirty %.1f us" % ((t3 - t2) / T * 1e6))
-    print("score_all_async + sync %.1f us" % ((t4 - t3) / T * 1e6))
+    for i in range(T):
+        f(i)
+    return (time.perf_counter() - t0) / T * 1e6
+
+
+def pass_only(i):
+    a = ctxs[i % R]; a.score_all_async(); a.sync()
+
+
+def upload_pass(i):
+    a = ctxs[i % R]; a.host_free_changed(); a.score_all_async(); a.sync()
+
+
+def sort_cycle(i):
+    a = ctxs[i % R]; a.host_free_changed(); a.ext_sort_inplace(1 + i % 8, pl)
+
+
+def sort_cycle_no_keys(i):
+    a = ctxs[i % R]; a.host_free_changed(); a.ext_sort_inplace(1 + i % 8, None)
+
+
+def sort_from_table(i):
+    a = ctxs[i % R]; a.ext_sort_inplace(1 + i % 8, pl)      # nothing changed: score kernel + sync only
+
+
+def sync_only(i):
+    ctxs[i % R].sync()
+
+
+print("sync alone                                  %6.1f us" % timed(sync_only))
+print("pass (masks resident) + sync                %6.1f us" % timed(pass_only))
+print("masks read in place by K0 + pass + sync     %6.1f us" % timed(upload_pass))
+print("full sort cycle (scores left by the pass)   %6.1f us" % timed(sort_cycle))
+print("full sort cycle without the placement keys  %6.1f us" % timed(sort_cycle_no_keys))
+for a in ctxs:
+    a.score_all(fetch=False)
+print("sort from the table (nothing changed)       %6.1f us" % timed(sort_from_table))
+for a in ctxs:
+    a.close()
