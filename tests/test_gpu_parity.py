@@ -537,3 +537,27 @@ def test_sort_scores_left_by_the_pass(gt, oracle, config, N):
             ln2 = m2 * (m2 - 1) // 2
             want2 = [0 if b == ol.INFEASIBLE else oracle.score_int(int(b) >> 16, ln2, cmax) for b in want_best[:, m2 - 1]]
             assert (a.host_scores() == np.array(want2, np.uint8)).all()
+
+
+def test_pipeline_form_of_k1_matches_the_oracle():
+    """k_score_pipe (GT_PIPE=1, an opt-in experiment: DESIGN.md section 3) must stay bit-exact while it is kept."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import _pkg, oracle_lib\n"
+        "gt = _pkg.load_package(); o = oracle_lib.load()\n"
+        "for cfg, n in ((4, 30000), (3, 6000), (33, 5000)):\n"
+        "    lv, ng, fr, _ = o.synth_cluster(cfg, 77 + n, 0, n)\n"
+        "    with gt.Allocator(n) as a:\n"
+        "        a.load_nodes(lv, ng, fr)\n"
+        "        got = a.score_all(); keys = a.best_node(np.arange(1, 17, dtype=np.uint8))\n"
+        "    want, _ = o.exhaustive_cluster(lv, ng, fr, o.lut(0), 8)\n"
+        "    assert (got == want).all() and (keys == o.cluster_argmin(want)).all(), cfg\n"
+        "print('pipe ok')\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GT_PIPE="1")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "pipe ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
