@@ -33,7 +33,7 @@ EXPORTS = [
     "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
     "gt_level_from_p2plink", "gt_levels_from_p2plink", "gt_lut_cmax",
     "gt_time_pass_rotated", "gt_best_node_local", "gt_comm_share",
-    "gt_host_free", "gt_host_free_changed", "gt_host_scores",
+    "gt_host_free", "gt_host_free_changed", "gt_host_scores", "gt_score_all_async_many",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -172,6 +172,8 @@ def _lib():
         L.gt_host_free_changed.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.gt_host_scores.argtypes = [C.c_void_p]
         L.gt_host_scores.restype = C.POINTER(C.c_uint8)
+    if hasattr(L, "gt_score_all_async_many"):
+        L.gt_score_all_async_many.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32]
     L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
     L.gt_schedule.argtypes = [C.c_void_p, u8p, u32p, C.c_uint32, u32p, u16p, u64p]
@@ -451,6 +453,14 @@ class Allocator:
     def comm_init(self, unique_id, rank, world):
         uid = np.ascontiguousarray(unique_id, np.uint8)
         self._ck(self._L.gt_comm_init(self._h, _p(uid, u8p), rank, world), "gt_comm_init")
+
+
+def score_all_async_many(allocators, passes):
+    """`passes` scoring passes enqueued round-robin over the allocators in one call (no sync)."""
+    arr = (C.c_void_p * len(allocators))(*[a._h.value for a in allocators])
+    rc = _lib().gt_score_all_async_many(arr, len(allocators), passes)
+    if rc:
+        raise GtError(rc, "gt_score_all_async_many", "; ".join(_lib().gt_last_error(a._h).decode() for a in allocators[:1]))
 
 
 def time_pass_rotated(allocators, iters=64):

@@ -939,6 +939,17 @@ int gt_score_all_async(gt_ctx *c)
     return rc;
 }
 
+// a scoring loop without a trip through the caller's language per pass: passes enqueued round-robin over the contexts
+int gt_score_all_async_many(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes)
+{
+    if (!ctxs || !n_ctx) return GT_ERR_INVALID;
+    for (uint32_t i = 0; i < passes; i++) {
+        int rc = gt_score_all_async(ctxs[i % n_ctx]);
+        if (rc != GT_OK) return rc;
+    }
+    return GT_OK;
+}
+
 int gt_sync(gt_ctx *c)
 {
     if (!c) return GT_ERR_INVALID;
