@@ -2,7 +2,7 @@
 """bench.py -- candidate GPU subsets scored per second on the topology-aware allocation path.
 
 A step is one Prioritize pass (design.md:118) over this rank's shard of a synthetic cluster:
-K0 k_bin (bin nodes by popcount(free)) -> K1 k_score_pipe (score every k-subset of every node's free set, per-node
+K0 k_bin (bin nodes by popcount(free)) -> K1 k_score (score every k-subset of every node's free set, per-node
 argmin, cluster argmin folded in) (+ a 128-byte min-exchange of the placement keys across ranks when N > 1).
 Workload: BASELINE.json config 4 (heterogeneous 100k-node cluster).  `value` is the weak-scaling figure
 (100 000 nodes PER GPU: nodes are independent); `strong` beside it is BASELINE's config 4
@@ -426,7 +426,7 @@ def main():
             pass
         traffic = (hw["dram_bytes_read"] + hw["dram_bytes_write"]) if hw else None
         roofline = {
-            "kernel": "k_score_pipe (K1 + folded cluster argmin)", "bound": "alu",
+            "kernel": "k_score (K1 + folded cluster argmin)", "bound": "alu",
             "achieved": alg_adds / t_cold / 1e9, "peak": peak_adds / 1e9, "unit": "Gadd/s",
             "frac": (alg_adds / t_cold) / peak_adds,
             "frac_l2warm": (alg_adds / t_warm) / peak_adds,
