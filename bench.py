@@ -207,6 +207,7 @@ def main():
                 a.comm_init(uid.cpu().numpy(), rank, world)
             elif world > 1:
                 a.comm_share(out[0]["ctx"])       # one communicator and one set of peer inboxes for all replicas
+            a.score_all(fetch=False)          # set-up, not warm-up: first pass of the context (all ranks: it carries an exchange)
             s, ad = a.count_subsets()
             out.append({"ctx": a, "subsets": s, "adds": ad, "free": fr, "n_gpus": n, "levels": lv if r == 0 else None})
         return out

@@ -1704,8 +1704,9 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     const unsigned long long *keys = out_place ? cluster_keys(c) : c->place_cur;
     // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them; launched as
     // programmatic dependents of the pass, so their launch latency is spent while K1 still runs
+    static const uint32_t scores_cta = getenv("GT_SCORES_CTA") ? (uint32_t)atoi(getenv("GT_SCORES_CTA")) : (uint32_t)gt::kCta;   // profiling aid
     cudaLaunchConfig_t cfg = {};
-    cfg.blockDim = dim3(gt::kCta);
+    cfg.blockDim = dim3(scores_cta);
     cfg.stream = c->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -1716,12 +1717,12 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     const unsigned long long *xerr = c->d_xflags + 3;
     if (c->scores_m == m) {
         const uint32_t threads = (c->n_nodes + 15) / 16;
-        cfg.gridDim = dim3((std::max(threads, 32u) + gt::kCta - 1) / gt::kCta);
+        cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_scores_out, (const uint8_t *)c->d_scores, (const uint32_t *)c->d_best, c->n_nodes, m,
                                       cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map), keys, okeys, xerr));
     } else {
         const uint32_t threads = (c->n_nodes + 3) / 4;
-        cfg.gridDim = dim3((std::max(threads, 32u) + gt::kCta - 1) / gt::kCta);
+        cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_sort_scores, (const uint32_t *)c->d_best, c->n_nodes, m, cmax, c->d_scores_map,
                                       keys, okeys, xerr));
     }
