@@ -702,15 +702,8 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             {
                 const uint32_t row = lane & 15u;
                 __syncwarp();
-#if GT_SMALL_SMEM == 2
-                // every lane copies the rows of its own node's free GPUs: p copy instructions per unit (all lanes of a
-                // unit have the same p), no shuffles; each touches 32 lines, one per lane
-                for (uint32_t r = f; r; r &= r - 1) {
-                    const uint32_t g = (uint32_t)__ffs(r) - 1u;
-                    copy16_async(ws.raw + lane * kTileStride + g * 16, prm.cost + (size_t)node * 256 + g * 16);
-                }
-                (void)row;
-#else
+                // (every lane copying the rows of its own node instead -- p copy instructions, no shuffles, 32 lines
+                // each -- measured 0.2 us slower per pass: profiles/r2_cold_ab_staging_occupancy_scorecta.txt)
 #pragma unroll
                 for (int t = 0; t < 16; t++) {       // asynchronous copies, all in flight together: one round trip
                     const int s2 = 2 * t + (int)(lane >> 4);
@@ -719,7 +712,6 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                     if ((ff >> row) & 1u)
                         copy16_async(ws.raw + s2 * kTileStride + row * 16, prm.cost + (size_t)nd * 256 + row * 16);
                 }
-#endif
                 copies_landed();
                 __syncwarp();
             }
