@@ -60,9 +60,9 @@ def workload_config(args, world, subsets_per_step):
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons of one GPU with NVML while the measurement runs."""
 
-    def __init__(self, index, period=0.02):
+    def __init__(self, index, period=0.02, start_delay=0.0):
         super().__init__(daemon=True)
-        self.index, self.period = index, period
+        self.index, self.period, self.start_delay = index, period, start_delay
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._halt = threading.Event()
         self.ok = False
@@ -86,6 +86,8 @@ class ClockSampler(threading.Thread):
             getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
             getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
         }
+        if self.start_delay:
+            time.sleep(self.start_delay)
         while not self._halt.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
@@ -233,9 +235,9 @@ def main():
         R = len(reps)
         cs = [r["ctx"] for r in reps]
         gt.score_all_async_many(cs, warmup)
-        barrier()
         l0 = sum(r["ctx"].launch_count for r in reps)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
         e0.record(stream)
         gt.score_all_async_many(cs, steps)      # pass i on replica i % R; one call, so the host pays two launches per pass
         e1.record(stream)
@@ -251,8 +253,9 @@ def main():
     subsets = [r["subsets"] for r in reps]
     read_mb = R * (N * 256 + N * 64) / 1e6
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler = ClockSampler(local_rank, start_delay=float(os.environ.get("GT_BENCH_SAMPLER_DELAY", "0")))
+    if not os.environ.get("GT_BENCH_NO_SAMPLER"):
+        sampler.start()
 
     # ---- device-resident throughput (`value`): inputs already in HBM
     ms, total_subsets, launches = timed_passes(reps, args.steps, args.warmup)

@@ -1715,16 +1715,24 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     cfg.numAttrs = 1;
     unsigned long long *okeys = out_place ? c->d_place_map : nullptr;
     const unsigned long long *xerr = c->d_xflags + 3;
+    // GT_SCORES_DMA=1 (experiment): the kernels finish the score bytes on the device and a copy-engine transfer brings
+    // them to the reply buffer, instead of the SMs storing into mapped host memory
+    static const bool scores_dma = getenv("GT_SCORES_DMA") != nullptr;
+    uint32_t *out_dev = scores_dma ? reinterpret_cast<uint32_t *>(c->d_scores) : c->d_scores_map;
     if (c->scores_m == m) {
         const uint32_t threads = (c->n_nodes + 15) / 16;
         cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_scores_out, (const uint8_t *)c->d_scores, (const uint32_t *)c->d_best, c->n_nodes, m,
-                                      cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(c->d_scores_map), keys, okeys, xerr));
+                                      cmax * (m * (m - 1) / 2), reinterpret_cast<uint4 *>(out_dev), keys, okeys, xerr));
     } else {
         const uint32_t threads = (c->n_nodes + 3) / 4;
         cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
-        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_sort_scores, (const uint32_t *)c->d_best, c->n_nodes, m, cmax, c->d_scores_map,
+        GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_sort_scores, (const uint32_t *)c->d_best, c->n_nodes, m, cmax, out_dev,
                                       keys, okeys, xerr));
+    }
+    if (scores_dma) {
+        GT_CUDA(c, cudaMemcpyAsync(c->h_scores, c->d_scores, ((size_t)c->n_nodes + 15) / 16 * 16, cudaMemcpyDeviceToHost, c->stream));
+        c->scores_m = m;        // the device bytes are final for this request size now
     }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
