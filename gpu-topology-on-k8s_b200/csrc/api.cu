@@ -1704,7 +1704,9 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     const unsigned long long *keys = out_place ? cluster_keys(c) : c->place_cur;
     // the kernels store scores and keys into mapped pinned memory: no device-to-host copy behind them; launched as
     // programmatic dependents of the pass, so their launch latency is spent while K1 still runs
-    static const uint32_t scores_cta = getenv("GT_SCORES_CTA") ? (uint32_t)atoi(getenv("GT_SCORES_CTA")) : (uint32_t)gt::kCta;   // profiling aid
+    // (block sizes of 32 / 64 threads instead of 256, and finishing the bytes on the device for a copy-engine transfer
+    // instead of storing into mapped memory, were measured: no change / 4.5 us slower per cycle, profiles/r2_scores_dma_ab.txt)
+    const uint32_t scores_cta = (uint32_t)gt::kCta;
     cudaLaunchConfig_t cfg = {};
     cfg.blockDim = dim3(scores_cta);
     cfg.stream = c->stream;
@@ -1715,10 +1717,7 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     cfg.numAttrs = 1;
     unsigned long long *okeys = out_place ? c->d_place_map : nullptr;
     const unsigned long long *xerr = c->d_xflags + 3;
-    // GT_SCORES_DMA=1 (experiment): the kernels finish the score bytes on the device and a copy-engine transfer brings
-    // them to the reply buffer, instead of the SMs storing into mapped host memory
-    static const bool scores_dma = getenv("GT_SCORES_DMA") != nullptr;
-    uint32_t *out_dev = scores_dma ? reinterpret_cast<uint32_t *>(c->d_scores) : c->d_scores_map;
+    uint32_t *out_dev = c->d_scores_map;
     if (c->scores_m == m) {
         const uint32_t threads = (c->n_nodes + 15) / 16;
         cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
@@ -1729,10 +1728,6 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
         cfg.gridDim = dim3((std::max(threads, 32u) + scores_cta - 1) / scores_cta);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_sort_scores, (const uint32_t *)c->d_best, c->n_nodes, m, cmax, out_dev,
                                       keys, okeys, xerr));
-    }
-    if (scores_dma) {
-        GT_CUDA(c, cudaMemcpyAsync(c->h_scores, c->d_scores, ((size_t)c->n_nodes + 15) / 16 * 16, cudaMemcpyDeviceToHost, c->stream));
-        c->scores_m = m;        // the device bytes are final for this request size now
     }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
