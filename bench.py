@@ -360,7 +360,11 @@ def main():
             sys.stderr.write("bench.py: sort scores differ from the oracle on the %d-node sample\n" % sample)
             raise SystemExit(3)
         checks["oracle_sample_scores"] = sample
+    keys_from_sort = place_np.copy()
     checks["exchange_checked_e2e"] = check_exchange(reps[elast], "after the e2e loop")
+    if not (keys_from_sort == ctxs[elast].best_node(ks)).all():      # what the sort call itself handed back
+        sys.stderr.write("bench.py rank %d: placement keys returned by gt_ext_sort differ from gt_best_node\n" % rank)
+        raise SystemExit(3)
 
     # the same cycle for a caller with ordinary buffers: masks memcpy'd into the mirror, scores memcpy'd out
     def cycle_copying(i):

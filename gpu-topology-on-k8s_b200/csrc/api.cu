@@ -413,27 +413,29 @@ gt::XWork x_step_for_pass(gt_ctx *c, uint64_t s)
     return w;
 }
 
-int launch_exchange_step(gt_ctx *c, const gt::XWork &w)
+int launch_exchange_step(gt_ctx *c, const gt::XWork &w, cudaStream_t on = nullptr)
 {
     if (!w.world) return GT_OK;
-    gt::k_exchange_step<<<1, 32, 0, c->stream>>>(w);
+    gt::k_exchange_step<<<1, 32, 0, on ? on : c->stream>>>(w);
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
     return GT_OK;
 }
 
-// somebody wants the cluster-wide keys of the latest pass: whatever of reduce(L-1), post(L), reduce(L) is still open
-int x_consume(gt_ctx *c)
+// somebody wants the cluster-wide keys of the latest pass: whatever of reduce(L-1), post(L), reduce(L) is still open.
+// keys_host / on: the step also hands the keys to the caller's mapped buffer and runs on another stream (gt_ext_sort).
+int x_consume(gt_ctx *c, unsigned long long *keys_host = nullptr, cudaStream_t on = nullptr)
 {
     const uint64_t L = c->x_seq;
     if (!L || c->x_reduced >= L) return GT_OK;
     gt::XWork w = x_blank(c);
+    w.keys_host = keys_host;
     w.world = (uint32_t)c->world;
     if (L >= 2 && c->x_reduced < L - 1) { w.seq_reduce1 = L - 1; w.out1 = x_global(c, L - 1); }
     if (c->x_posted < L) { w.seq_post = L; w.post_keys = x_local(c, L); }
     w.seq_reduce2 = L; w.out2 = x_global(c, L);
     c->x_posted = c->x_reduced = L;
-    return launch_exchange_step(c, w);
+    return launch_exchange_step(c, w, on);
 }
 
 // where the placement keys a caller may see are: the cluster-wide ones with peers, else what the pass left
@@ -1696,8 +1698,15 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     if (rc != GT_OK) return rc;
     if (!c->n_nodes) return GT_OK;
     const uint32_t cmax = gt_lut_cmax(c->lut);
-    if (out_place && lazy_exchange(c)) {
-        if ((rc = x_consume(c)) != GT_OK) return rc;
+    bool keys_by_step = false;
+    if (out_place && lazy_exchange(c) && c->x_seq && c->x_reduced < c->x_seq) {
+        // the exchange of the pass that just went out runs on the communication stream, beside the score write-back, and
+        // hands the keys to the reply buffer itself
+        GT_CUDA(c, cudaEventRecord(c->ev_pass, c->stream));
+        GT_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_pass, 0));
+        if ((rc = x_consume(c, c->d_place_map, c->comm_stream)) != GT_OK) return rc;
+        GT_CUDA(c, cudaEventRecord(c->ev_comm[0], c->comm_stream));
+        keys_by_step = true;
     } else if (out_place && c->comm && c->comm_last >= 0) {
         GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[c->comm_last], 0));
     }
@@ -1715,7 +1724,7 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    unsigned long long *okeys = out_place ? c->d_place_map : nullptr;
+    unsigned long long *okeys = (out_place && !keys_by_step) ? c->d_place_map : nullptr;
     const unsigned long long *xerr = c->d_xflags + 3;
     uint32_t *out_dev = c->d_scores_map;
     if (c->scores_m == m) {
@@ -1731,6 +1740,7 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     }
     c->launches++;
     GT_CUDA(c, cudaGetLastError());
+    if (keys_by_step) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[0], 0));   // later passes stay behind the exchange
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
     if (out_scores) memcpy(out_scores, c->h_scores, c->n_nodes);   // NULL: the caller reads gt_host_scores() in place
     if (out_place) {

@@ -51,6 +51,7 @@ struct XWork {
     unsigned long long *inbox[kMaxPeers];   // inbox base of every rank (own address for the own rank); world == 0: no work
     const unsigned long long *post_keys;    // this rank's 16 keys of pass `seq_post`
     unsigned long long *out1, *out2;        // where the cluster-wide keys of passes seq_reduce1 / seq_reduce2 go
+    unsigned long long *keys_host;          // optional: mapped host memory, receives the 16 keys of seq_reduce2 + err_flag's word
     unsigned long long *err_flag;           // pass number of a reduction that gave up waiting for a peer
     unsigned long long seq_reduce1, seq_post, seq_reduce2;   // 0 = nothing to do
     uint32_t rank, world;
@@ -195,6 +196,10 @@ __device__ __forceinline__ void exchange_step(const XWork &w, uint32_t lane)
     }
     reduce(w.seq_reduce2, w.out2);
     __syncwarp();
+    if (w.keys_host) {       // the caller's copy, straight from here: the score write-back runs beside this kernel
+        if (lane < 16) w.keys_host[lane] = w.out2[lane];
+        if (lane == 16) w.keys_host[16] = *reinterpret_cast<volatile unsigned long long *>(w.err_flag);
+    }
 }
 
 __global__ void __launch_bounds__(32) k_exchange_step(XWork w)
@@ -264,6 +269,9 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     if (tid == 0) GT_KT_MIN(5, gt_now());
 #endif
     if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
+    // (fetching the CTA's 256 masks as 32 16-byte loads by one warp -- one 512-byte PCIe read instead of eight 64-byte
+    // ones when the mirror is read in place -- was measured: 0.3 us slower per resident pass for the extra barrier,
+    // no gain end to end: profiles/r2_k0_wide_loads_ab.txt)
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
     int p = -1;
