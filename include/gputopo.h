@@ -307,13 +307,20 @@ int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_gpus, const 
                           uint32_t n_nodes, uint32_t *d_best, void *stream, char *err_buf, size_t err_len);
 
 /* ---- multi-GPU: nodes are sharded, one context per GPU; the only exchange is a min over 16 keys ---- */
+/* One process per GPU; rank 0 makes the id, every rank calls gt_comm_init with it.  From then on the 16 placement keys
+ * of every pass are min-combined over the ranks: gt_best_node and gt_ext_sort(.., out_place) return the cluster's
+ * winners (replaces nothing in the reference -- kube-scheduler picks the host there, design.md:115-119).  All ranks
+ * must issue the same sequence of passes and key requests on a context.  A peer that does not show up within 2 s
+ * turns the call that wanted the keys into GT_ERR_STATE; nothing on the GPU waits without a time limit. */
 int gt_comm_unique_id(uint8_t out_id[128]);
 int gt_comm_init(gt_ctx *ctx, const uint8_t id[128], int rank, int world);
-/* further contexts of one process on the same device (other clusters, replicas) join the communicator of `owner`
- * instead of creating their own; all ranks must do the same, and `owner` must be destroyed last */
+/* further contexts of one process on the same device (other clusters, replicas) join the NCCL communicator of `owner`
+ * instead of creating their own (they get an inbox of their own for the peer-memory exchange, so their passes stay
+ * independent); collective: all ranks share the same way, in the same order; `owner` must be destroyed last */
 int gt_comm_share(gt_ctx *ctx, gt_ctx *owner);
-/* how the placement keys travel between ranks: 0 = no communicator, 1 = NCCL all-reduce, 2 = own kernel over peer
- * memory (ranks are separate processes on one NVLink domain that could map each other's inbox through CUDA IPC) */
+/* how the placement keys travel between ranks: 0 = no communicator, 1 = NCCL all-reduce on a side stream, 2 = peer
+ * memory over NVLink (ranks are separate processes that could map each other's inbox through CUDA IPC): the work
+ * rides on one warp of the scoring kernel of the following passes and on the call that asks for the keys */
 int gt_comm_mode(const gt_ctx *ctx);
 
 /* ---- synthetic clusters for tests and benchmarks (splitmix64) ---- */
