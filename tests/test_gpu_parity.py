@@ -561,3 +561,29 @@ def test_pipeline_form_of_k1_matches_the_oracle():
     env = dict(os.environ, GT_PIPE="1")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "pipe ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+def test_scoring_loop_in_one_call_and_local_keys(gt, oracle):
+    """gt_score_all_async_many over several contexts = the same passes one by one; gt_best_node_local (K2 over the
+    table) agrees with the keys K1 folded; the in-place K1 timing runs and leaves the contexts usable."""
+    import torch
+    stream = torch.cuda.Stream()
+    ctxs, wants = [], []
+    for r in range(3):
+        lv, n, fr, _ = oracle.synth_cluster(4, 0xA11 + r, 0, 7000)
+        a = gt.Allocator(7000, stream=stream.cuda_stream)
+        a.load_nodes(lv, n, fr)
+        ctxs.append(a)
+        wants.append(oracle.exhaustive_cluster(lv, n, fr, oracle.lut(0), 4)[0])
+    gt.score_all_async_many(ctxs, 7)
+    ks = np.arange(1, 17, dtype=np.uint8)
+    for a, want in zip(ctxs, wants):
+        keys = a.best_node(ks)
+        assert (keys == oracle.cluster_argmin(want)).all()
+        assert (a.best_node_local() == keys).all()
+        assert (a.score_all() == want).all()
+    rest, k1, whole = gt.time_pass_rotated(ctxs, 12)
+    assert 0 < k1 < whole < 1000 and rest > 0
+    for a, want in zip(ctxs, wants):
+        assert (a.score_all() == want).all()
+        a.close()
