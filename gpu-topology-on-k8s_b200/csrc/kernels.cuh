@@ -667,11 +667,21 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // ptxas turns an atomic add on a provably warp-uniform address (even from inline PTX, even atom.inc) into
     // a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once -- that stalled every
     // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
-    const uint32_t n_warps = gridDim.x * (kScoreCta / 32);
-    if (prm.xw.world && blockIdx.x == 0 && warp == kScoreCta / 32 - 1) exchange_step(prm.xw, lane);   // multi-GPU, see there
+    // Multi-GPU: the last warp of CTA 0 carries the exchange step of the two passes before this one (see exchange_step).
+    // It gets no unit of its own to start with -- the step costs it 2-3 us of NVLink round trips, and a unit waiting
+    // behind that would end the kernel late -- and joins the others through the ticket afterwards.
+    const uint32_t gw = blockIdx.x * (kScoreCta / 32) + warp, xw_warp = kScoreCta / 32 - 1;
+    const bool has_x = prm.xw.world != 0;
+    const uint32_t n_warps = gridDim.x * (kScoreCta / 32) - (has_x ? 1u : 0u);   // warps that start on a unit of their own
     // (dealing the first units round-robin over the CTAs, or handing the longest units out first, measured slower
     // both with warm and with cold L2: profiles/r2_cold_ab_orders_staging.txt)
-    uint32_t u = blockIdx.x * (kScoreCta / 32) + warp;
+    uint32_t u = has_x && gw > xw_warp ? gw - 1 : gw;
+    if (has_x && gw == xw_warp) {
+        exchange_step(prm.xw, lane);
+        uint32_t t = 0;
+        if (lane == 0) t = take_ticket(prm, lane);
+        u = __shfl_sync(0xFFFFFFFFu, t, 0) + n_warps;
+    }
     int i = 0;
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
