@@ -683,16 +683,32 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         u = __shfl_sync(0xFFFFFFFFu, t, 0) + n_warps;
     }
     int i = 0;
+#ifndef GT_BIN_LOOKUP_BALLOT
+#define GT_BIN_LOOKUP_BALLOT 1
+#endif
+#if GT_BIN_LOOKUP_BALLOT
+    const uint32_t my_end = lane < (uint32_t)kBins ? s_end[lane] : 0xFFFFFFFFu;
+    const uint32_t my_cnt = lane < (uint32_t)kBins ? s_cnt[bin_order((int)lane)] : 0u;   // count of the bin at hand-out position `lane`
+#endif
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
     while (u < total) {
         uint32_t next = 0;
         if (!GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);
         // `next` is not touched again before the end of this unit: the reply has a whole unit to arrive
+#if GT_BIN_LOOKUP_BALLOT
+        // which bin: lane l keeps the cumulative unit count after hand-out position l, one ballot instead of a walk
+        // through shared memory (a chain of dependent loads in front of every unit)
+        i = __popc(__ballot_sync(0xFFFFFFFFu, lane < (uint32_t)kBins && u >= my_end));
+        const int p = bin_order(i);
+        const uint32_t lu = u - (i ? __shfl_sync(0xFFFFFFFFu, my_end, i - 1) : 0u);
+        const uint32_t cnt = __shfl_sync(0xFFFFFFFFu, my_cnt, i);
+#else
         while (u >= s_end[i]) i++;            // units only grow: continue from the previous bin
         const int p = bin_order(i);
         const uint32_t lu = u - (i ? s_end[i - 1] : 0u);
         const uint32_t cnt = s_cnt[p];
+#endif
         GT_TR(32 + p);   // unit start
         if (p > 8) {
 #ifdef GT_TRACE
@@ -722,13 +738,24 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 __syncwarp();
                 // (every lane copying the rows of its own node instead -- p copy instructions, no shuffles, 32 lines
                 // each -- measured 0.2 us slower per pass: profiles/r2_cold_ab_staging_occupancy_scorecta.txt)
+                if (!__any_sync(0xFFFFFFFFu, f >> 8)) {      // rows 0..7 only: four nodes per copy instruction
 #pragma unroll
-                for (int t = 0; t < 16; t++) {       // asynchronous copies, all in flight together: one round trip
-                    const int s2 = 2 * t + (int)(lane >> 4);
-                    const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, s2);
-                    const uint32_t ff = __shfl_sync(0xFFFFFFFFu, f, s2);     // 0 for slots beyond the bin's end
-                    if ((ff >> row) & 1u)
-                        copy16_async(ws.raw + s2 * kTileStride + row * 16, prm.cost + (size_t)nd * 256 + row * 16);
+                    for (int t = 0; t < 8; t++) {
+                        const int s2 = 4 * t + (int)(lane >> 3);
+                        const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, s2);
+                        const uint32_t ff = __shfl_sync(0xFFFFFFFFu, f, s2);
+                        if ((ff >> (lane & 7u)) & 1u)
+                            copy16_async(ws.raw + s2 * kTileStride + (lane & 7u) * 16, prm.cost + (size_t)nd * 256 + (lane & 7u) * 16);
+                    }
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 16; t++) {       // asynchronous copies, all in flight together: one round trip
+                        const int s2 = 2 * t + (int)(lane >> 4);
+                        const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, s2);
+                        const uint32_t ff = __shfl_sync(0xFFFFFFFFu, f, s2);     // 0 for slots beyond the bin's end
+                        if ((ff >> row) & 1u)
+                            copy16_async(ws.raw + s2 * kTileStride + row * 16, prm.cost + (size_t)nd * 256 + row * 16);
+                    }
                 }
                 copies_landed();
                 __syncwarp();
