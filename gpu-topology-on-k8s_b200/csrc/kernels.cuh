@@ -589,12 +589,16 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
         WarpBest hb2;
         hb2.v = kInf; hb2.node = 0xFFFFFFFFu;
-        for (uint32_t s2 = lane >> 4; s2 < live; s2 += 2) {
-            const uint32_t nd = __ldg(list + first + s2);
-            const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
-            prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
-            if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
-            hb2.take(v, nd);
+        for (uint32_t s0 = 0; s0 < live; s0 += 2) {       // (uniform trip count: the shuffle needs the whole warp)
+            const uint32_t s2 = s0 + (lane >> 4);
+            // the node of slot s2 sits in the registers of that slot's lanes: no second trip to the bin list
+            const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, (int)((s2 << hb) & 31u));
+            if (s2 < live) {
+                const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
+                prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+                if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
+                hb2.take(v, nd);
+            }
         }
         __syncwarp();
         const uint32_t ov = __shfl_xor_sync(0xFFFFFFFFu, hb2.v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, hb2.node, 16);
@@ -619,7 +623,6 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 {
     __shared__ WarpScratch s_ws[kScoreCta / 32];
     __shared__ unsigned long long s_place[16];
-    __shared__ uint32_t s_cnt[kBins], s_end[kBins];   // s_end[i]: cumulative units after bin bin_order(i)
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 #ifdef GT_TRACE
     unsigned long long *tr = prm.trace + (size_t)(blockIdx.x * (kScoreCta / 32) + warp) * kTraceSlots;
@@ -637,17 +640,17 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 #ifdef GT_TRACE
     if (tid == 0) { GT_KT_MIN(2, kt_entry); GT_KT_MIN(3, gt_now()); }
 #endif
-    // units per bin in hand-out order, then an inclusive scan inside warp 0 (17 lanes)
-    if (warp == 0) {
-        uint32_t units = 0, cnt = 0;
-        int p = 0;
+    // units per bin in hand-out order and their inclusive scan, in every warp for itself (17 lanes, registers only):
+    // nobody waits at a barrier for one warp's round trip to the control block
+    uint32_t my_cnt = 0, my_end = 0;
+    {
+        uint32_t units = 0;
         if (lane < (uint32_t)kBins) {
-            p = bin_order((int)lane);
-            cnt = prm.ctl[p];
-            s_cnt[p] = cnt;
-            if (p >= kSplitP) units = cnt << (p - 13);
-            else if (p > 8) units = (cnt + (32u >> (p - 8)) - 1) >> (13 - p);
-            else units = (cnt + 31u) >> 5;
+            const int p = bin_order((int)lane);
+            my_cnt = prm.ctl[p];
+            if (p >= kSplitP) units = my_cnt << (p - 13);
+            else if (p > 8) units = (my_cnt + (32u >> (p - 8)) - 1) >> (13 - p);
+            else units = (my_cnt + 31u) >> 5;
 #ifdef GT_BINMASK   // profiling builds only: score just the bins in the mask (results are incomplete)
             if (!((GT_BINMASK >> p) & 1u)) units = 0;
 #endif
@@ -657,10 +660,10 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, units, d);
             if (lane >= (uint32_t)d) units += o;
         }
-        if (lane < (uint32_t)kBins) s_end[lane] = units;
+        my_end = lane < (uint32_t)kBins ? units : 0xFFFFFFFFu;
     }
-    __syncthreads();
-    const uint32_t total = s_end[kBins - 1];
+    __syncthreads();      // s_place is set
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, my_end, kBins - 1);
     WarpScratch &ws = s_ws[warp];
     GT_TR(3);
     // first unit = this warp's global index; later ones come from the ticket, requested one unit ahead.
@@ -682,33 +685,19 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         if (lane == 0) t = take_ticket(prm, lane);
         u = __shfl_sync(0xFFFFFFFFu, t, 0) + n_warps;
     }
-    int i = 0;
-#ifndef GT_BIN_LOOKUP_BALLOT
-#define GT_BIN_LOOKUP_BALLOT 1
-#endif
-#if GT_BIN_LOOKUP_BALLOT
-    const uint32_t my_end = lane < (uint32_t)kBins ? s_end[lane] : 0xFFFFFFFFu;
-    const uint32_t my_cnt = lane < (uint32_t)kBins ? s_cnt[bin_order((int)lane)] : 0u;   // count of the bin at hand-out position `lane`
-#endif
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
     while (u < total) {
         uint32_t next = 0;
         if (!GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);
         // `next` is not touched again before the end of this unit: the reply has a whole unit to arrive
-#if GT_BIN_LOOKUP_BALLOT
-        // which bin: lane l keeps the cumulative unit count after hand-out position l, one ballot instead of a walk
-        // through shared memory (a chain of dependent loads in front of every unit)
-        i = __popc(__ballot_sync(0xFFFFFFFFu, lane < (uint32_t)kBins && u >= my_end));
+        // which bin: lane l keeps the cumulative unit count after hand-out position l and that bin's node count; one
+        // ballot instead of a walk through shared memory (a chain of dependent loads in front of every unit: 0.35 us per
+        // pass, profiles/r2_ballot_lookup_ab.txt)
+        const int i = __popc(__ballot_sync(0xFFFFFFFFu, lane < (uint32_t)kBins && u >= my_end));
         const int p = bin_order(i);
         const uint32_t lu = u - (i ? __shfl_sync(0xFFFFFFFFu, my_end, i - 1) : 0u);
         const uint32_t cnt = __shfl_sync(0xFFFFFFFFu, my_cnt, i);
-#else
-        while (u >= s_end[i]) i++;            // units only grow: continue from the previous bin
-        const int p = bin_order(i);
-        const uint32_t lu = u - (i ? s_end[i - 1] : 0u);
-        const uint32_t cnt = s_cnt[p];
-#endif
         GT_TR(32 + p);   // unit start
         if (p > 8) {
 #ifdef GT_TRACE
