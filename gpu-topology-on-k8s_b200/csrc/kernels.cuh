@@ -109,6 +109,10 @@ __host__ __device__ constexpr int bin_order_host(int i)
 #ifndef GT_BIN_ORDER
 #define GT_BIN_ORDER 0
 #endif
+#ifndef GT_MIX_FROM
+#define GT_MIX_FROM 0
+#define GT_MIX_TO 0
+#endif
 #if GT_BIN_ORDER == 0
     constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
 #else                     // longest measured unit first
@@ -589,16 +593,14 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
         WarpBest hb2;
         hb2.v = kInf; hb2.node = 0xFFFFFFFFu;
-        for (uint32_t s0 = 0; s0 < live; s0 += 2) {       // (uniform trip count: the shuffle needs the whole warp)
-            const uint32_t s2 = s0 + (lane >> 4);
-            // the node of slot s2 sits in the registers of that slot's lanes: no second trip to the bin list
-            const uint32_t nd = __shfl_sync(0xFFFFFFFFu, node, (int)((s2 << hb) & 31u));
-            if (s2 < live) {
-                const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
-                prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
-                if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
-                hb2.take(v, nd);
-            }
+        // (node ids re-read from the bin list, an L1 hit: taking them from the registers of the slot's lanes with a
+        //  shuffle measured 0.1 us per pass slower, profiles/r2_writeout_ab.txt)
+        for (uint32_t s2 = lane >> 4; s2 < live; s2 += 2) {
+            const uint32_t nd = __ldg(list + first + s2);
+            const uint32_t v = ws.best[s2][(lane & 15u) + 1u];
+            prm.best[(size_t)nd * 16 + (lane & 15u)] = v;
+            if (prm.score_k == (lane & 15u) + 1u) prm.scores[nd] = (uint8_t)score_byte(v, prm.score_den);
+            hb2.take(v, nd);
         }
         __syncwarp();
         const uint32_t ov = __shfl_xor_sync(0xFFFFFFFFu, hb2.v, 16), on = __shfl_xor_sync(0xFFFFFFFFu, hb2.node, 16);
@@ -655,6 +657,10 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
             if (!((GT_BINMASK >> p) & 1u)) units = 0;
 #endif
         }
+#ifdef GT_TRACE
+        if (__any_sync(0xFFFFFFFFu, units == 0xFFFFFFF1u)) GT_TR(99);
+        GT_TR(6);    // control block arrived
+#endif
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, units, d);
@@ -662,6 +668,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         }
         my_end = lane < (uint32_t)kBins ? units : 0xFFFFFFFFu;
     }
+    GT_TR(7);    // scan done
     __syncthreads();      // s_place is set
     const uint32_t total = __shfl_sync(0xFFFFFFFFu, my_end, kBins - 1);
     WarpScratch &ws = s_ws[warp];
@@ -687,9 +694,20 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     }
     WarpBest wb;
     wb.v = kInf; wb.node = 0xFFFFFFFFu;
+#if GT_MIX_FROM
+    // hand-out positions [0, GT_MIX_FROM) (long, issue-bound units) alternate with positions [GT_MIX_FROM, GT_MIX_TO]
+    // (short, latency-bound units) until one of the two runs out; what is left follows in order
+    const uint32_t mix_a = __shfl_sync(0xFFFFFFFFu, my_end, GT_MIX_FROM - 1);
+    const uint32_t mix_b = __shfl_sync(0xFFFFFFFFu, my_end, GT_MIX_TO) - mix_a;
+    const uint32_t mix_m = min(mix_a, mix_b);
+#endif
     while (u < total) {
         uint32_t next = 0;
         if (!GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);
+#if GT_MIX_FROM
+        if (u < 2u * mix_m) u = (u & 1u) ? mix_a + (u >> 1) : (u >> 1);
+        else if (mix_a > mix_b && u - 2u * mix_b < mix_a - mix_b) u -= mix_b;
+#endif
         // `next` is not touched again before the end of this unit: the reply has a whole unit to arrive
         // which bin: lane l keeps the cumulative unit count after hand-out position l and that bin's node count; one
         // ballot instead of a walk through shared memory (a chain of dependent loads in front of every unit: 0.35 us per

@@ -14,6 +14,13 @@ gt = _pkg.load_package()
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 100000
 lv, ng, fr, _ = gt.synth_cluster(4, 0x5EED0004, 0, N)
 SL = 64
+COLD = int(os.environ.get("GT_TRACE_COLD", "0"))     # this many other clusters pass in between (their tables evict ours from L2)
+others = []
+for r in range(COLD):
+    lv2, ng2, fr2, _ = gt.synth_cluster(4, 0x5EED0104 + r, 0, N)
+    o = gt.Allocator(N)
+    o.load_nodes(lv2, ng2, fr2)
+    others.append(o)
 with gt.Allocator(N) as a:
     a.load_nodes(lv, ng, fr)
     for _ in range(3):
@@ -22,9 +29,17 @@ with gt.Allocator(N) as a:
     L.gt_debug_trace.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32]
     nw = 148 * 8 * 4
     buf = np.zeros(nw * SL, np.uint64)
+    for o in others:
+        o.score_all(fetch=False)
     L.gt_debug_trace(a._h, buf.ctypes.data_as(C.POINTER(C.c_uint64)), len(buf))   # clear
+    for o in others:
+        o.score_all(fetch=False)
+        L.gt_debug_trace(o._h, buf.ctypes.data_as(C.POINTER(C.c_uint64)), len(buf))
     a.score_all(fetch=False)
     L.gt_debug_trace(a._h, buf.ctypes.data_as(C.POINTER(C.c_uint64)), len(buf))
+for o in others:
+    o.close()
+print("other clusters scored in between:", COLD)
 tr = buf.reshape(nw, SL)
 t = (tr >> np.uint64(8)).astype(np.int64)
 ev = (tr & np.uint64(0xFF)).astype(np.int64)
@@ -37,8 +52,8 @@ units_per_warp = []
 for w in np.nonzero(used)[0]:
     e, tt = ev[w], t[w]
     n = int((tr[w] != 0).sum())
-    marks = {int(e[i]): int(tt[i]) for i in range(n) if e[i] in (1, 2, 3, 4, 5)}
-    for k in (1, 2, 3, 4, 5):
+    marks = {int(e[i]): int(tt[i]) for i in range(n) if e[i] in (1, 2, 3, 4, 5, 6, 7)}
+    for k in (1, 2, 6, 7, 3, 4, 5):
         if k in marks:
             phase[k].append(marks[k] - t0)
     cnt = 0
@@ -49,7 +64,7 @@ for w in np.nonzero(used)[0]:
             start = int(tt[i])
             j = i + 1
             sub = {}
-            while j < n and e[j] < 32 and e[j] not in (4, 5):
+            while j < n and e[j] < 32 and e[j] not in (4, 5, 6, 7):
                 sub[int(e[j])] = int(tt[j])
                 j += 1
             end = sub.get(14, sub.get(13, start))
@@ -86,8 +101,10 @@ for pp in sorted(first, reverse=True):
     print("   p=%2d %5d %7d %7d" % (pp, len(v), np.median(v), v.max()))
 hist = np.histogram([f[0] for f in fin], bins=12)
 print("finish-time histogram:", list(zip(hist[1][:-1].astype(int), hist[0])))
-names = {1: "kernel entry", 2: "after griddep wait", 3: "after ctl+barriers", 4: "work loop done", 5: "after final barrier"}
-for k in (1, 2, 3, 4, 5):
+names = {1: "kernel entry", 2: "after griddep wait", 6: "control block arrived", 7: "scan done", 3: "after the barrier", 4: "work loop done", 5: "after final barrier"}
+for k in (1, 2, 6, 7, 3, 4, 5):
+    if not phase[k]:
+        continue
     v = np.array(phase[k])
     print("%-22s min %7d  median %7d  max %7d ns" % (names[k], v.min(), np.median(v), v.max()))
 print("units per warp: mean %.2f max %d" % (np.mean(units_per_warp), max(units_per_warp)))
