@@ -120,6 +120,9 @@ struct gt_ctx {
     uint16_t *d_free_map = nullptr;             // device view of h_free (mapped): K0 reads a whole-shard update in place
     unsigned long long *ktime_next = nullptr;   // measurement: where the next K1 leaves its time stamps
     bool masks_in_place = false;                // the K0 being enqueued reads the masks from the mirror, not from d_free
+    bool k0_inputs_pending = true;              // a write to the device masks / GPU counts / id list has been queued since the last K0
+    uint32_t ctl_half = 0;                      // which of the two control blocks the next K0 / K1 pair uses (all zero between passes)
+    bool capturing = false;                     // kernels being recorded into a graph are replayed later: no per-call promises
     uint8_t *h_ngpus = nullptr;
     uint32_t *h_ids = nullptr;
     uint16_t *h_masks = nullptr;
@@ -208,6 +211,7 @@ int flush_free(gt_ctx *c, bool all)
 {
     if (!c->n_nodes) return GT_OK;
     if (all || !c->free_uploaded) {
+        c->k0_inputs_pending = true;
         GT_CUDA(c, cudaMemcpyAsync(c->d_free, c->h_free, (size_t)c->n_nodes * 2, cudaMemcpyHostToDevice, c->stream));
         GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
         c->h2d_pending = true;
@@ -222,6 +226,7 @@ int flush_free(gt_ctx *c, bool all)
         c->h_ids[i] = c->dirty[i];
         c->h_masks[i] = c->h_free[c->dirty[i]];
     }
+    c->k0_inputs_pending = true;
     GT_CUDA(c, cudaMemcpyAsync(c->d_ids, c->h_ids, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     GT_CUDA(c, cudaMemcpyAsync(c->d_masks, c->h_masks, (size_t)n * 2, cudaMemcpyHostToDevice, c->stream));
     k_scatter_free<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_ids, c->d_masks, n, c->d_free);
@@ -248,11 +253,13 @@ void mark_dirty(gt_ctx *c, uint32_t node)
 }
 
 unsigned long long *bin_place(gt_ctx *c, uint32_t parity) { return c->d_place + 32 + 16 * parity; }
+uint32_t *cur_ctl(gt_ctx *c) { return c->d_bin_cnt + c->ctl_half * gt::kCtlWords; }
 
 gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep_bins)
 {
     gt::ScoreParams p = {};
-    p.cost = c->d_cost; p.best = c->d_best; p.ctl = c->d_bin_cnt; p.bin_list = c->d_bin_list;
+    p.cost = c->d_cost; p.best = c->d_best; p.ctl = cur_ctl(c); p.bin_list = c->d_bin_list;
+    p.self_clean = 1u; p.ctl_next = nullptr;
     p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
     p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
     p.xw = gt::XWork{};
@@ -283,11 +290,16 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     static const bool no_pdl = getenv("GT_NO_PDL") != nullptr || getenv("GT_NO_PDL_K0") != nullptr;   // profiling aid
     cfg.numAttrs = no_pdl ? 0 : 1;
     const bool in_place = c->masks_in_place && !d_ids;
+    // whole-shard K0 whose inputs nothing in the queue is still writing: it may fetch and count the masks before its
+    // wait for the kernel in front of it, i.e. behind the tail of the previous pass's K1 (GT_NO_EARLY_K0: profiling aid)
+    static const bool no_early = getenv("GT_NO_EARLY_K0") != nullptr;
+    const uint32_t early = !no_pdl && !no_early && !d_ids && !c->k0_inputs_pending && !c->capturing ? 1u : 0u;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus,
                                   (const uint16_t *)(in_place ? c->d_free_map : c->d_free), d_ids, n,
-                                  c->cap, c->d_bin_cnt, c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
+                                  c->cap, cur_ctl(c), c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
                                   (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr),
-                                  (uint16_t *)(in_place ? c->d_free : nullptr)));
+                                  (uint16_t *)(in_place ? c->d_free : nullptr), early));
+    c->k0_inputs_pending = false;    // this K0, or its wait, is behind every write queued so far
     if (in_place) {       // the mirror may not change before this K0 has read it
         GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
         c->h2d_pending = true;
@@ -345,7 +357,16 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
         c->place_cur = fold;
         return GT_OK;
     }
+    // the two control blocks take turns (see k_score) unless this launch has to leave its own block usable again:
+    // timing runs that keep the bins or want the end-of-kernel stamp, and kernels recorded into a graph
+    static const bool no_flip = getenv("GT_NO_CTL_FLIP") != nullptr;     // profiling aid
+    const bool flip = !no_flip && !keep_bins && !prm.ktime && !c->capturing && !(c->flags & GT_FLAG_GRAPH);
+    if (flip) {
+        prm.self_clean = 0u;
+        prm.ctl_next = c->d_bin_cnt + (c->ctl_half ^ 1u) * gt::kCtlWords;
+    }
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, prm));
+    if (flip) c->ctl_half ^= 1u;
     c->launches++;
     if (fold) c->place_cur = fold;
     return GT_OK;
@@ -470,12 +491,14 @@ int launch_step_graph(gt_ctx *c, uint32_t parity)
         cudaGraph_t graph = nullptr;
         const uint64_t before = c->launches;
         GT_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        c->capturing = true;
         const uint32_t want = c->want_score_m;
         c->want_score_m = 0;            // the captured kernels are replayed for every later pass: no per-call parameters
         int rc = launch_bin(c, nullptr, c->n_nodes, bin_place(c, parity));
         if (rc == GT_OK) rc = launch_score(c, c->n_nodes, bin_place(c, parity));
         if (rc == GT_OK) rc = launch_singular(c, nullptr, c->n_nodes, bin_place(c, parity));
         cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        c->capturing = false;
         c->want_score_m = want;
         c->launches = before;
         if (rc != GT_OK || e != cudaSuccess || !graph) {
@@ -662,8 +685,8 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_sibling, N * 32));
         GT_CUDA(c, cudaMalloc(&c->d_free, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_best, N * 64));
-        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, gt::kCtlWords * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, 2 * gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, 2 * gt::kCtlWords * sizeof(uint32_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_free, (size_t)gt::kBins * N * sizeof(uint16_t)));
         GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
         GT_CUDA(c, cudaMalloc(&c->d_place, 128 * sizeof(unsigned long long)));
@@ -794,6 +817,7 @@ int gt_load_nodes(gt_ctx *c, uint32_t first, uint32_t count, const uint8_t *leve
         }
         c->classes_uploaded = false;
     }
+    c->k0_inputs_pending = true;
     GT_CUDA(c, cudaMemcpyAsync(c->d_ngpus + first, c->h_ngpus + first, count, cudaMemcpyHostToDevice, c->stream));
     GT_CUDA(c, cudaMemcpyAsync(c->d_free + first, c->h_free + first, (size_t)count * 2, cudaMemcpyHostToDevice, c->stream));
     if (access_cost)
@@ -1070,7 +1094,7 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     const uint32_t peak_iters = 2048;
     auto one = [&]() -> int {
         if (w == "bin") {   // K0 alone: its counters have to be cleared by hand between launches
-            GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
+            GT_CUDA(c, cudaMemsetAsync(cur_ctl(c), 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
             return launch_bin(c, nullptr, c->n_nodes, bin_place(c, 0));
         }
         if (w == "score") return launch_score(c, c->n_nodes, bin_place(c, 0), true);
@@ -1105,7 +1129,7 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     // leave the pipeline consistent: control block zero, best table and placement keys current
-    GT_CUDA(c, cudaMemsetAsync(c->d_bin_cnt, 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
+    GT_CUDA(c, cudaMemsetAsync(cur_ctl(c), 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
     if ((rc = enqueue_scoring(c, nullptr, c->n_nodes)) != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
     *out_ms = ms / (float)iters;
@@ -2015,7 +2039,7 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr, nullptr, nullptr);
+                                                                     nullptr, nullptr, nullptr, 0u);
     gt::ScoreParams prm = {};
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;

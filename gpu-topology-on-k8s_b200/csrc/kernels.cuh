@@ -67,6 +67,9 @@ struct ScoreParams {
     uint32_t cap, first_node;
     uint32_t fold_place;      // full pass: K1 folds its rows into place (K0 preset it)
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
+    uint32_t self_clean;      // 1: the last CTA to finish zeroes this control block (it costs every CTA an atomic round trip
+                              //    before it may exit); 0: the block stays as it is and ctl_next is the next pass's
+    uint32_t *ctl_next;       // the other control block, last used by the pass before this one: CTA 0 zeroes it (null: none)
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
     unsigned long long *ktime;      // measurement: [0] globaltimer when CTA 0 got past the dependency wait, [1] when the last CTA finished (null = off)
     XWork xw;                       // multi-GPU: exchange work of the two passes before this one, done by one warp of K1
@@ -258,7 +261,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
                                               unsigned long long *__restrict__ place, uint8_t *__restrict__ scores,
-                                              uint16_t *__restrict__ free_copy)
+                                              uint16_t *__restrict__ free_copy, uint32_t early)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
@@ -267,30 +270,37 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
 #endif
     if (tid < kBins) s_cnt[tid] = 0;
     // K0 is itself launched as a programmatic dependent of whatever kernel precedes it (normally the previous
-    // pass's K1): its CTAs become resident as that grid drains and wait here until it has completed and flushed.
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // pass's K1): its CTAs become resident as that grid drains and wait until it has completed and flushed.
+    // early != 0 (the host sets it when nothing queued in front of this launch writes the masks or the id list):
+    // the masks are fetched and counted BEFORE that wait, behind the tail of the previous kernel; everything that
+    // kernel may still read or write (control block, bin lists, best rows, scores, the device copy of the masks)
+    // is touched after it.
+    if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
 #ifdef GT_TRACE
     if (tid == 0) GT_KT_MIN(5, gt_now());
 #endif
-    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     // (fetching the CTA's 256 masks as 32 16-byte loads by one warp -- one 512-byte PCIe read instead of eight 64-byte
     // ones when the mirror is read in place -- was measured: 0.3 us slower per resident pass for the extra barrier,
     // no gain end to end: profiles/r2_k0_wide_loads_ab.txt)
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + tid;
     int p = -1;
-    uint32_t slot = 0, node = 0, f = 0;
+    uint32_t slot = 0, node = 0, f = 0, raw = 0;
     if (i < n) {
         node = ids ? ids[i] : i;
         uint32_t ng = n_gpus[node];
         ng = ng > (uint32_t)kMaxG ? (uint32_t)kMaxG : ng;
-        const uint32_t raw = free_mask[node];
-        // free_mask may be the caller's pinned host mirror read in place (whole-shard update): the device copy that
-        // later passes over single nodes read is refreshed on the way, no separate upload
-        if (free_copy) free_copy[node] = (uint16_t)raw;
+        raw = free_mask[node];
         f = raw & ((1u << ng) - 1u);
         p = __popc(f);
         slot = atomicAdd(&s_cnt[p], 1u);
+    }
+    if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
+    if (p >= 0) {
+        // free_mask may be the caller's pinned host mirror read in place (whole-shard update): the device copy that
+        // later passes over single nodes read is refreshed on the way, no separate upload
+        if (free_copy) free_copy[node] = (uint16_t)raw;
         if (p >= kSplitP) {   // several warp units of K1 meet in this row through atomicMin
             uint4 *o = reinterpret_cast<uint4 *>(best + (size_t)node * 16);
             const uint4 inf = make_uint4(kInf, kInf, kInf, kInf);
@@ -637,6 +647,9 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     if (tid < 16) s_place[tid] = ~0ull;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // K0's bins are complete and visible (no-op without PDL)
     if (prm.ktime && blockIdx.x == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prm.ktime[0]));
+    // two control blocks take turns: the one the previous pass used is free from here on (its K1 has completed) and
+    // is zeroed now for the next pass's K0, so that no CTA of this pass has to find out whether it is the last one
+    if (prm.ctl_next && blockIdx.x == 0 && tid < (uint32_t)kCtlWords) prm.ctl_next[tid] = 0u;
     GT_TR(2);
     if (GT_K1_TRIGGER == 1) asm volatile("griddepcontrol.launch_dependents;");
 #ifdef GT_TRACE
@@ -801,8 +814,8 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     __syncthreads();
     GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
-    // the last CTA to finish leaves the control block zeroed for the next pass
-    if (tid == 0) {
+    // self_clean: the last CTA to finish leaves the control block zeroed for the next pass
+    if (tid == 0 && prm.self_clean) {
 #ifdef GT_TRACE
         GT_KT_MAX(4, gt_now());
         __threadfence();

@@ -1,7 +1,12 @@
 export GT_NO_REBUILD=1
-for v in mixA mixB; do GT_LIB=ab/$v.so timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1; done
-GT_LIB=ab/trace2.so timeout 120 python tools/trace_k1.py > gpurun_out/r2_trace_warm.txt 2>&1
-GT_LIB=ab/trace2.so GT_TRACE_COLD=8 timeout 120 python tools/trace_k1.py > gpurun_out/r2_trace_cold.txt 2>&1
-for i in 1 2; do for v in main2 mixA mixB; do GT_LIB=ab/$v.so python bench.py --steps 2000 --warmup 50 --no-extras --no-cpu-baseline > gpurun_out/r2_mix_${v}_$i.json 2>/dev/null; done; done
-python tools/bench_brief.py gpurun_out/r2_mix_*.json | tee gpurun_out/r2_mix_ab.txt
-tools/ab_probe.sh "ab/main2.so ab/empty.so" 4 100000 2>&1 | tee gpurun_out/r2_empty_k1.txt
+export GT_LIB=ab/flip.so
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
+B="python bench.py --steps 2000 --warmup 50 --no-extras --no-cpu-baseline"
+for i in 1 2; do
+  GT_NO_EARLY_K0=1 GT_NO_CTL_FLIP=1 $B > gpurun_out/r2_hand_none_$i.json 2>/dev/null
+  GT_NO_CTL_FLIP=1 $B > gpurun_out/r2_hand_early_$i.json 2>/dev/null
+  GT_NO_EARLY_K0=1 $B > gpurun_out/r2_hand_flip_$i.json 2>/dev/null
+  $B > gpurun_out/r2_hand_both_$i.json 2>/dev/null
+done
+python tools/bench_brief.py gpurun_out/r2_hand_*.json | tee gpurun_out/r2_handover_ab.txt
+python bench.py --steps 20 --warmup 5 --no-extras --no-cpu-baseline 2>/dev/null | python tools/bench_brief.py /dev/stdin | tee -a gpurun_out/r2_handover_ab.txt
