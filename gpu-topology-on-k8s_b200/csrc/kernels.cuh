@@ -544,10 +544,14 @@ struct WarpScratch {
 // next unit number from the global ticket.  ptxas turns an atomic add on a provably warp-uniform address (even from
 // inline PTX, even atom.inc) into a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once:
 // the address therefore carries a run-time zero times the lane index.
+// Inside `if (lane == 0)` the compiler knows the lane and folds the product away again (cuobjdump: VOTEU / FLO / POPC /
+// @P0 ATOMG / SHFL.IDX right behind it: 0.5 us of waiting per unit).  So the whole warp executes the instruction under a
+// predicate and no branch tells the compiler which lane it is; lanes other than 0 get 0 back.
 __device__ __forceinline__ uint32_t take_ticket(const ScoreParams &prm, uint32_t lane)
 {
-    uint32_t next;
-    asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(next) : "l"(prm.ctl + kCtlTicket + prm.zero * lane) : "memory");
+    uint32_t next = 0;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %2, 0;\n\t@p atom.global.add.u32 %0, [%1], 1;\n\t}"
+                 : "+r"(next) : "l"(prm.ctl + kCtlTicket + prm.zero * lane), "r"(lane) : "memory");
     return next;
 }
 
@@ -597,7 +601,7 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     GT_TR(11);   // tiles staged
     if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
     __syncwarp();
-    if (GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);   // the reply arrives during the write-out
+    if (GT_LATE_TICKET) next = take_ticket(prm, lane);   // (lane 0 only, see there) the reply arrives during the write-out
     GT_TR(12);   // set-up + tree + atomics done
     if (hb <= 5) {
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
@@ -702,7 +706,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     if (has_x && gw == xw_warp) {
         exchange_step(prm.xw, lane);
         uint32_t t = 0;
-        if (lane == 0) t = take_ticket(prm, lane);
+        t = take_ticket(prm, lane);
         u = __shfl_sync(0xFFFFFFFFu, t, 0) + n_warps;
     }
     WarpBest wb;
@@ -716,7 +720,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
 #endif
     while (u < total) {
         uint32_t next = 0;
-        if (!GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);
+        if (!GT_LATE_TICKET) next = take_ticket(prm, lane);
 #if GT_MIX_FROM
         if (u < 2u * mix_m) u = (u & 1u) ? mix_a + (u >> 1) : (u >> 1);
         else if (mix_a > mix_b && u - 2u * mix_b < mix_a - mix_b) u -= mix_b;
@@ -794,7 +798,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 o[3] = make_uint4(kInf, kInf, kInf, kInf);
                 if (prm.score_k) prm.scores[node] = (uint8_t)score_byte(pick_row(out, prm.score_k), prm.score_den);
             }
-            if (GT_LATE_TICKET && lane == 0) next = take_ticket(prm, lane);   // the reply arrives during the fold
+            if (GT_LATE_TICKET) next = take_ticket(prm, lane);   // (lane 0 only) the reply arrives during the fold
             if (prm.fold_place) {
                 fold_small_warp4<0>(wb, out, node, lane);
                 if (p > 4) fold_small_warp4<4>(wb, out, node, lane);
