@@ -121,7 +121,9 @@ struct gt_ctx {
     unsigned long long *ktime_next = nullptr;   // measurement: where the next K1 leaves its time stamps
     bool masks_in_place = false;                // the K0 being enqueued reads the masks from the mirror, not from d_free
     bool k0_inputs_pending = true;              // a write to the device masks / GPU counts / id list has been queued since the last K0
-    uint32_t ctl_half = 0;                      // which of the two control blocks the next K0 / K1 pair uses (all zero between passes)
+    uint32_t ctl_idx = 0;                       // which of the three control blocks the next K0 / K1 pair uses (zero between passes)
+    uint32_t list_half = 0;                     // which of the two sets of bin lists the next K0 / K1 pair uses
+    bool k0_may_run_ahead = false;              // the last K1 launched rotated blocks and lists: the next K0 touches nothing it reads
     bool capturing = false;                     // kernels being recorded into a graph are replayed later: no per-call promises
     uint8_t *h_ngpus = nullptr;
     uint32_t *h_ids = nullptr;
@@ -253,14 +255,16 @@ void mark_dirty(gt_ctx *c, uint32_t node)
 }
 
 unsigned long long *bin_place(gt_ctx *c, uint32_t parity) { return c->d_place + 32 + 16 * parity; }
-uint32_t *cur_ctl(gt_ctx *c) { return c->d_bin_cnt + c->ctl_half * gt::kCtlWords; }
+uint32_t *cur_ctl(gt_ctx *c) { return c->d_bin_cnt + c->ctl_idx * gt::kCtlWords; }
+uint32_t *cur_list(gt_ctx *c) { return c->d_bin_list + (size_t)c->list_half * gt::kBins * c->cap; }
+uint16_t *cur_flist(gt_ctx *c) { return c->d_bin_free + (size_t)c->list_half * gt::kBins * c->cap; }
 
 gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep_bins)
 {
     gt::ScoreParams p = {};
-    p.cost = c->d_cost; p.best = c->d_best; p.ctl = cur_ctl(c); p.bin_list = c->d_bin_list;
-    p.self_clean = 1u; p.ctl_next = nullptr;
-    p.bin_free = c->d_bin_free; p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
+    p.cost = c->d_cost; p.best = c->d_best; p.ctl = cur_ctl(c); p.bin_list = cur_list(c);
+    p.self_clean = 1u; p.ctl_next = nullptr; p.trigger_early = 0u;
+    p.bin_free = cur_flist(c); p.place = fold_into; p.cap = c->cap; p.first_node = c->first_node;
     p.fold_place = fold_into ? 1u : 0u; p.keep_bins = keep_bins ? 1u : 0u; p.zero = 0;
     p.xw = gt::XWork{};
     p.scores = nullptr; p.score_k = 0; p.score_den = 0;
@@ -293,10 +297,14 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
     // whole-shard K0 whose inputs nothing in the queue is still writing: it may fetch and count the masks before its
     // wait for the kernel in front of it, i.e. behind the tail of the previous pass's K1 (GT_NO_EARLY_K0: profiling aid)
     static const bool no_early = getenv("GT_NO_EARLY_K0") != nullptr;
-    const uint32_t early = !no_pdl && !no_early && !d_ids && !c->k0_inputs_pending && !c->capturing ? 1u : 0u;
+    // ... and when the K1 in front of it works on the other set of bin lists and another control block (see
+    // launch_score), K0 also reserves its ranges and fills its lists before the wait: 2 (GT_NO_K0_AHEAD: level 1 at most)
+    static const bool no_ahead = getenv("GT_NO_K0_AHEAD") != nullptr;
+    uint32_t early = !no_pdl && !no_early && !d_ids && !c->k0_inputs_pending && !c->capturing ? 1u : 0u;
+    if (early && c->k0_may_run_ahead && !no_ahead) early = 2u;
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_bin, (const uint8_t *)c->d_ngpus,
                                   (const uint16_t *)(in_place ? c->d_free_map : c->d_free), d_ids, n,
-                                  c->cap, cur_ctl(c), c->d_bin_list, c->d_bin_free, c->d_best, preset_place,
+                                  c->cap, cur_ctl(c), cur_list(c), cur_flist(c), c->d_best, preset_place,
                                   (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr),
                                   (uint16_t *)(in_place ? c->d_free : nullptr), early));
     c->k0_inputs_pending = false;    // this K0, or its wait, is behind every write queued so far
@@ -353,6 +361,7 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
         cfg.blockDim = dim3(gt::pipe::kCta);
         cfg.dynamicSmemBytes = sizeof(gt::pipe::Shared);
         GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score_pipe, prm));
+        c->k0_may_run_ahead = false;
         c->launches++;
         c->place_cur = fold;
         return GT_OK;
@@ -362,11 +371,19 @@ int launch_score(gt_ctx *c, uint32_t n, unsigned long long *fold, bool keep_bins
     static const bool no_flip = getenv("GT_NO_CTL_FLIP") != nullptr;     // profiling aid
     const bool flip = !no_flip && !keep_bins && !prm.ktime && !c->capturing && !(c->flags & GT_FLAG_GRAPH);
     if (flip) {
+        // three blocks in rotation: this pass's, the next pass's (zeroed by the K1 before this one, so the next K0 may
+        // count into it while this K1 still runs) and the one the pass before this used, which this K1 zeroes
         prm.self_clean = 0u;
-        prm.ctl_next = c->d_bin_cnt + (c->ctl_half ^ 1u) * gt::kCtlWords;
+        prm.ctl_next = c->d_bin_cnt + ((c->ctl_idx + 2u) % 3u) * gt::kCtlWords;
+        static const bool no_ahead = getenv("GT_NO_K0_AHEAD") != nullptr;
+        prm.trigger_early = no_ahead ? 0u : 1u;   // dependents may become resident as this grid's CTAs leave
     }
     GT_CUDA(c, cudaLaunchKernelEx(&cfg, gt::k_score, prm));
-    if (flip) c->ctl_half ^= 1u;
+    if (flip) {
+        c->ctl_idx = (c->ctl_idx + 1u) % 3u;
+        c->list_half ^= 1u;
+    }
+    c->k0_may_run_ahead = flip;
     c->launches++;
     if (fold) c->place_cur = fold;
     return GT_OK;
@@ -685,10 +702,10 @@ int gt_create(const gt_config *cfg, gt_ctx **out)
         GT_CUDA(c, cudaMalloc(&c->d_sibling, N * 32));
         GT_CUDA(c, cudaMalloc(&c->d_free, N * 2));
         GT_CUDA(c, cudaMalloc(&c->d_best, N * 64));
-        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, 2 * gt::kCtlWords * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, 2 * gt::kCtlWords * sizeof(uint32_t)));
-        GT_CUDA(c, cudaMalloc(&c->d_bin_free, (size_t)gt::kBins * N * sizeof(uint16_t)));
-        GT_CUDA(c, cudaMalloc(&c->d_bin_list, (size_t)gt::kBins * N * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_cnt, 3 * gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMemset(c->d_bin_cnt, 0, 3 * gt::kCtlWords * sizeof(uint32_t)));
+        GT_CUDA(c, cudaMalloc(&c->d_bin_free, 2 * (size_t)gt::kBins * N * sizeof(uint16_t)));   // two sets: K0 of the next pass
+        GT_CUDA(c, cudaMalloc(&c->d_bin_list, 2 * (size_t)gt::kBins * N * sizeof(uint32_t)));   // fills one while K1 reads the other
         GT_CUDA(c, cudaMalloc(&c->d_place, 128 * sizeof(unsigned long long)));
         GT_CUDA(c, cudaMemset(c->d_place, 0xFF, 128 * sizeof(unsigned long long)));
         c->place_cur = c->d_place + 32;

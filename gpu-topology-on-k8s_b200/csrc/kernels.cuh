@@ -69,7 +69,9 @@ struct ScoreParams {
     uint32_t keep_bins;       // timing runs: leave the bin counts for another launch
     uint32_t self_clean;      // 1: the last CTA to finish zeroes this control block (it costs every CTA an atomic round trip
                               //    before it may exit); 0: the block stays as it is and ctl_next is the next pass's
-    uint32_t *ctl_next;       // the other control block, last used by the pass before this one: CTA 0 zeroes it (null: none)
+    uint32_t *ctl_next;       // the control block the pass before this one used: CTA 0 zeroes it for the pass after next (null: none)
+    uint32_t trigger_early;   // 1: dependents may be scheduled once every CTA is past its wait (they become resident as
+                              //    CTAs leave: a K0 that runs ahead, see k_bin); 0: once every CTA has finished its units
     uint32_t zero;            // always 0: keeps the ticket address from looking warp-uniform to ptxas (see k_score)
     unsigned long long *ktime;      // measurement: [0] globaltimer when CTA 0 got past the dependency wait, [1] when the last CTA finished (null = off)
     XWork xw;                       // multi-GPU: exchange work of the two passes before this one, done by one warp of K1
@@ -295,7 +297,20 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
         p = __popc(f);
         slot = atomicAdd(&s_cnt[p], 1u);
     }
-    if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (early == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
+    // early == 2: the kernel in front is a K1 that reads the other set of bin lists and another control block (this
+    // one was zeroed a pass ago): ranges are reserved and lists filled before the wait as well, so that a K0 whose CTAs
+    // became resident while that K1 was still finishing its last units has only the presets below left to do
+    __syncthreads();
+    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&ctl[tid], s_cnt[tid]);
+    __syncthreads();
+    if (p >= 0) {
+        const size_t at = (size_t)p * cap + s_base[p] + slot;
+        bin_list[at] = node;
+        bin_free[at] = (uint16_t)f;
+    }
+    if (early == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
+    // what the previous pass's kernels may still have been reading or writing
     if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
     if (p >= 0) {
         // free_mask may be the caller's pinned host mirror read in place (whole-shard update): the device copy that
@@ -307,14 +322,6 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
             o[0] = inf; o[1] = inf; o[2] = inf; o[3] = inf;
             if (scores) scores[node] = (uint8_t)kScorePending;
         }
-    }
-    __syncthreads();
-    if (tid < kBins && s_cnt[tid]) s_base[tid] = atomicAdd(&ctl[tid], s_cnt[tid]);
-    __syncthreads();
-    if (p >= 0) {
-        const size_t at = (size_t)p * cap + s_base[p] + slot;
-        bin_list[at] = node;
-        bin_free[at] = (uint16_t)f;
     }
     // programmatic dependent launch: from here on K1's CTAs may be scheduled while this grid drains; K1 waits
     // (griddepcontrol.wait) for the whole grid before it reads the bins.  Triggering at the top of K0 instead
@@ -655,7 +662,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     // is zeroed now for the next pass's K0, so that no CTA of this pass has to find out whether it is the last one
     if (prm.ctl_next && blockIdx.x == 0 && tid < (uint32_t)kCtlWords) prm.ctl_next[tid] = 0u;
     GT_TR(2);
-    if (GT_K1_TRIGGER == 1) asm volatile("griddepcontrol.launch_dependents;");
+    if (GT_K1_TRIGGER == 1 || prm.trigger_early) asm volatile("griddepcontrol.launch_dependents;");
 #ifdef GT_TRACE
     if (tid == 0) { GT_KT_MIN(2, kt_entry); GT_KT_MIN(3, gt_now()); }
 #endif
@@ -814,7 +821,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
         atomicMin(&s_place[lane], key);
     }
     GT_TR(4);
-    if (GT_K1_TRIGGER == 2) asm volatile("griddepcontrol.launch_dependents;");
+    if (GT_K1_TRIGGER == 2 && !prm.trigger_early) asm volatile("griddepcontrol.launch_dependents;");
     __syncthreads();
     GT_TR(5);
     if (prm.fold_place && tid < 16 && s_place[tid] != ~0ull) atomicMin(prm.place + tid, s_place[tid]);
