@@ -587,3 +587,54 @@ def test_scoring_loop_in_one_call_and_local_keys(gt, oracle):
     for a, want in zip(ctxs, wants):
         assert (a.score_all() == want).all()
         a.close()
+
+
+def test_masks_change_between_passes_that_are_not_waited_for(gt, oracle):
+    """K0 of a pass runs ahead of the previous pass's K1 (other set of bin lists, other control block).  Every kind of
+    mask update in between -- in place in the pinned mirror, uploaded, single nodes through commit -- must leave exactly
+    the table of the LAST masks, and passes of several contexts interleaved on one stream must not disturb each other."""
+    import torch
+    N = 30000
+    ks = np.arange(1, 17, dtype=np.uint8)
+    lv, n, fr, _ = oracle.synth_cluster(4, 0xBEE5, 0, N)
+    rng = np.random.default_rng(77)
+    full = ((1 << n.astype(np.uint32)) - 1).astype(np.uint16)
+    draws = [(rng.integers(0, 1 << 16, N).astype(np.uint16) & full) for _ in range(7)]
+    stream = torch.cuda.Stream()
+    with gt.Allocator(N, stream=stream.cuda_stream) as a, gt.Allocator(N, stream=stream.cuda_stream) as b:
+        a.load_nodes(lv, n, fr)
+        b.load_nodes(lv, n, draws[6])
+        a.score_all_async()
+        for i in range(6):                        # no synchronisation between these passes
+            if i % 3 == 0:
+                a.host_free()[:N] = draws[i]      # read in place by the next K0
+                a.host_free_changed()
+            elif i % 3 == 1:
+                a.update_free(draws[i])           # whole-shard update through the caller's buffer
+            else:
+                a.host_free()[:N] = draws[i]
+                a.host_free_changed()
+                a.score_all_async()
+                a.score_all_async()               # the same masks again: K0 fully ahead of the K1 in front
+            b.score_all_async()                   # another cluster's pass in between, same stream
+            a.score_all_async()
+        want = oracle.exhaustive_cluster(lv, n, draws[5], oracle.lut(0), 8)[0]
+        got = a.score_all()
+        bad = np.nonzero((got != want).any(axis=1))[0]
+        assert len(bad) == 0, "first mismatch node %d" % bad[0]
+        assert (a.best_node(ks) == oracle.cluster_argmin(want)).all()
+        want_b = oracle.exhaustive_cluster(lv, n, draws[6], oracle.lut(0), 8)[0]
+        assert (b.best_node(ks) == oracle.cluster_argmin(want_b)).all()
+        assert (b.score_all() == want_b).all()
+        # single-node changes, a dirty pass, then full passes again
+        free_now = draws[5].copy()
+        nodes = np.nonzero(free_now)[0][:50].astype(np.uint32)
+        masks = np.array([int(free_now[i]) & -int(free_now[i]) for i in nodes], np.uint16)     # lowest free GPU of each
+        a.commit(nodes, masks)
+        free_now[nodes] &= ~masks
+        a.score_dirty()
+        a.score_all_async()
+        a.score_all_async()
+        want2 = oracle.exhaustive_cluster(lv, n, free_now, oracle.lut(0), 8)[0]
+        assert (a.score_all() == want2).all()
+        assert (a.best_node(ks) == oracle.cluster_argmin(want2)).all()
