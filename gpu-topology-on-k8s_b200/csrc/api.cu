@@ -77,9 +77,9 @@ struct gt_ctx {
     uint32_t *d_best = nullptr;
     uint32_t *d_bin_cnt = nullptr, *d_bin_list = nullptr;   // scratch of K0/K1 (control block, node lists)
     uint16_t *d_bin_free = nullptr;                         // scratch: free masks beside the node lists
-    unsigned long long *d_place = nullptr;      // [8][16]: [1] scratch of gt_best_node_local, [2],[3] the two key buffers K1 folds into, [4],[5] the cluster-wide keys of the two latest passes (peer-memory exchange)
+    unsigned long long *d_place = nullptr;      // [8][16]: [1] scratch of gt_best_node_local, [2],[3],[6] the key buffers K1 folds into, [4],[5],[7] the cluster-wide keys of the three latest passes (peer-memory exchange)
     unsigned long long *place_cur = nullptr;    // where the latest placement keys are
-    cudaGraphExec_t step_exec[2] = {nullptr, nullptr};   // captured K0 + K1 of a full pass, per place parity
+    cudaGraphExec_t step_exec[3] = {nullptr, nullptr, nullptr};   // captured K0 + K1 of a full pass, per key buffer
     uint32_t step_nodes = 0;                    // n_nodes the graphs were captured for
     bool graph_failed = false;
     uint32_t bin_parity = 0;                    // placement-key buffer the next pass writes
@@ -254,7 +254,9 @@ void mark_dirty(gt_ctx *c, uint32_t node)
     c->place_valid = false;
 }
 
-unsigned long long *bin_place(gt_ctx *c, uint32_t parity) { return c->d_place + 32 + 16 * parity; }
+// key buffer K1 folds into: rows [2], [3] and [6] of d_place (two alternate without peers, three rotate with the
+// peer-memory exchange, where the keys of a pass are posted a pass later than they are produced)
+unsigned long long *bin_place(gt_ctx *c, uint32_t slot) { return c->d_place + (slot == 2 ? 96 : 32 + 16 * slot); }
 uint32_t *cur_ctl(gt_ctx *c) { return c->d_bin_cnt + c->ctl_idx * gt::kCtlWords; }
 uint32_t *cur_list(gt_ctx *c) { return c->d_bin_list + (size_t)c->list_half * gt::kBins * c->cap; }
 uint16_t *cur_flist(gt_ctx *c) { return c->d_bin_free + (size_t)c->list_half * gt::kBins * c->cap; }
@@ -279,12 +281,14 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
 }
 
 // K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
-int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place)
+int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place, const gt::XWork *xw = nullptr)
 {
     // programmatic dependent of the kernel in front of it (the previous pass's K1 in a scoring loop): the launch
     // latency between two passes is spent while that kernel still runs; K0 waits inside for its completion
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((n + gt::kCta - 1) / gt::kCta);
+    // multi-GPU: CTA 0 is an extra one that carries a step of the key exchange (k_bin)
+    const gt::XWork xwork = xw ? *xw : gt::XWork{};
+    cfg.gridDim = dim3((n + gt::kCta - 1) / gt::kCta + (xwork.world ? 1u : 0u));
     cfg.blockDim = dim3(gt::kCta);
     cfg.stream = c->stream;
     cudaLaunchAttribute attr[1];
@@ -306,7 +310,7 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
                                   (const uint16_t *)(in_place ? c->d_free_map : c->d_free), d_ids, n,
                                   c->cap, cur_ctl(c), cur_list(c), cur_flist(c), c->d_best, preset_place,
                                   (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr),
-                                  (uint16_t *)(in_place ? c->d_free : nullptr), early));
+                                  (uint16_t *)(in_place ? c->d_free : nullptr), early, xwork));
     c->k0_inputs_pending = false;    // this K0, or its wait, is behind every write queued so far
     if (in_place) {       // the mirror may not change before this K0 has read it
         GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
@@ -420,8 +424,8 @@ int exchange_min(gt_ctx *c, unsigned long long *place, uint32_t parity)
 
 // ---- Multi-GPU over peer memory: the exchange is piggybacked on the passes (kernels.cuh, exchange_step).
 // Key buffers of pass number s: this rank's own keys (what K1 folds into) and the cluster-wide result.
-unsigned long long *x_local(gt_ctx *c, uint64_t s) { return c->d_place + 32 + 16 * (s & 1u); }
-unsigned long long *x_global(gt_ctx *c, uint64_t s) { return c->d_place + 64 + 16 * (s & 1u); }
+unsigned long long *x_local(gt_ctx *c, uint64_t s) { return bin_place(c, (uint32_t)(s % 3u)); }
+unsigned long long *x_global(gt_ctx *c, uint64_t s) { const uint32_t q = (uint32_t)(s % 3u); return c->d_place + (q == 2 ? 112 : 64 + 16 * q); }
 bool lazy_exchange(const gt_ctx *c) { return c->comm && c->p2p; }
 
 gt::XWork x_blank(gt_ctx *c)
@@ -434,19 +438,23 @@ gt::XWork x_blank(gt_ctx *c)
     return w;
 }
 
-// the exchange work that goes with pass s: reduce(s-2), then post(s-1)
-gt::XWork x_step_for_pass(gt_ctx *c, uint64_t s)
+// Protocol state of this rank: its keys of passes 1..x_posted are in every inbox, the cluster-wide keys of passes
+// 1..x_reduced are in x_global; x_reduced <= x_posted <= x_reduced + 1.  One step (exchange_step) is, in this order,
+// reduce(x_reduced + 1) if that pass is posted, post(x_posted + 1), reduce of the pass just posted -- each only as far
+// as the caller's bounds allow (a pass can be posted once its K1 is complete).
+gt::XWork x_next(gt_ctx *c, uint64_t max_post, uint64_t max_reduce)
 {
     gt::XWork w = x_blank(c);
-    if (s >= 3 && c->x_reduced < s - 2) {
-        w.seq_reduce1 = s - 2; w.out1 = x_global(c, s - 2);
-        c->x_reduced = s - 2;
+    if (c->x_reduced < c->x_posted && c->x_reduced + 1 <= max_reduce) {
+        const uint64_t s = ++c->x_reduced;
+        w.seq_reduce1 = s; w.out1 = x_global(c, s);
         w.world = (uint32_t)c->world;
     }
-    if (s >= 2 && c->x_posted < s - 1) {
-        w.seq_post = s - 1; w.post_keys = x_local(c, s - 1);
-        c->x_posted = s - 1;
+    if (c->x_posted == c->x_reduced && c->x_posted + 1 <= max_post) {
+        const uint64_t s = ++c->x_posted;
+        w.seq_post = s; w.post_keys = x_local(c, s);
         w.world = (uint32_t)c->world;
+        if (s <= max_reduce) { w.seq_reduce2 = s; w.out2 = x_global(c, s); c->x_reduced = s; }
     }
     return w;
 }
@@ -460,20 +468,31 @@ int launch_exchange_step(gt_ctx *c, const gt::XWork &w, cudaStream_t on = nullpt
     return GT_OK;
 }
 
-// somebody wants the cluster-wide keys of the latest pass: whatever of reduce(L-1), post(L), reduce(L) is still open.
-// keys_host / on: the step also hands the keys to the caller's mapped buffer and runs on another stream (gt_ext_sort).
+// one-warp kernels until the protocol is at (max_post, max_reduce) or as far as it can get
+int x_catch_up(gt_ctx *c, uint64_t max_post, uint64_t max_reduce, cudaStream_t on = nullptr)
+{
+    for (;;) {
+        gt::XWork w = x_next(c, max_post, max_reduce);
+        if (!w.world) return GT_OK;
+        int rc = launch_exchange_step(c, w, on);
+        if (rc != GT_OK) return rc;
+    }
+}
+
+// somebody wants the cluster-wide keys of the latest pass: whatever is still open, in one-warp kernels.
+// keys_host / on: the last step also hands the keys to the caller's mapped buffer; they run on another stream (gt_ext_sort).
 int x_consume(gt_ctx *c, unsigned long long *keys_host = nullptr, cudaStream_t on = nullptr)
 {
     const uint64_t L = c->x_seq;
-    if (!L || c->x_reduced >= L) return GT_OK;
-    gt::XWork w = x_blank(c);
-    w.keys_host = keys_host;
-    w.world = (uint32_t)c->world;
-    if (L >= 2 && c->x_reduced < L - 1) { w.seq_reduce1 = L - 1; w.out1 = x_global(c, L - 1); }
-    if (c->x_posted < L) { w.seq_post = L; w.post_keys = x_local(c, L); }
-    w.seq_reduce2 = L; w.out2 = x_global(c, L);
-    c->x_posted = c->x_reduced = L;
-    return launch_exchange_step(c, w, on);
+    if (!L) return GT_OK;
+    while (c->x_reduced < L) {
+        gt::XWork w = x_next(c, L, L);
+        if (!w.world) break;
+        if (c->x_reduced >= L) w.keys_host = keys_host;
+        int rc = launch_exchange_step(c, w, on);
+        if (rc != GT_OK) return rc;
+    }
+    return GT_OK;
 }
 
 // where the placement keys a caller may see are: the cluster-wide ones with peers, else what the pass left
@@ -598,11 +617,19 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
     const bool graph = !d_ids && n && (c->flags & GT_FLAG_GRAPH) && !c->graph_failed;
     // with peers over peer memory the pass has a number, its key buffers go by that number, and the exchange work of
     // the two passes before it rides on its K1 (or, on the paths without a K1 of their own, in a one-warp kernel)
-    const bool lazy = lazy_exchange(c);
+    static const bool probe_no_x = getenv("GT_PROBE_NO_EXCHANGE") != nullptr;   // timing probe: passes of a rank with peers, nothing exchanged
+    const bool lazy = lazy_exchange(c) && !probe_no_x;
     const uint64_t seq = lazy ? c->x_seq + 1 : 0;
-    gt::XWork step = lazy ? x_step_for_pass(c, seq) : gt::XWork{};
-    const uint32_t par = lazy ? (uint32_t)(seq & 1u) : c->bin_parity;
+    const uint32_t par = lazy ? (uint32_t)(seq % 3u) : c->bin_parity;
     if ((rc = wait_place_free(c, par)) != GT_OK) return rc;
+    // Plain K0 -> K1 passes: one warp of K1 carries the step, reduce(seq-2) and post(seq-1).  GT_X_ON_K0: an extra CTA
+    // of K0 instead, before K0's dependency wait, i.e. beside the last units of the previous K1 -- what it may post then
+    // is the pass before the previous one, reduce(seq-3) and post(seq-2).  Parity-clean, but the step's NVLink round
+    // trips (2-3 us) outlast the tail of that K1 and K0 ends late: 1 us per pass slower (profiles/r2_mp_probe_v4.txt).
+    // Either way the key buffer this pass folds into last held pass seq-3, which must be posted before K0 presets it.
+    static const bool x_on_k1 = getenv("GT_X_ON_K0") == nullptr;
+    if (lazy && seq > 4 && (rc = x_catch_up(c, seq - 3, seq - 4)) != GT_OK) return rc;
+    gt::XWork step = gt::XWork{};
     c->scores_m = 0;
     bool step_taken = false;
     if (!d_ids && n) {
@@ -618,8 +645,9 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
             if (!done) c->graph_failed = true;   // capture unavailable (e.g. the stream is being captured): plain launches
         }
         if (!done) {
-            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
-            if ((rc = launch_score(c, n, bin_place(c, par), false, step.world ? &step : nullptr)) != GT_OK) return rc;
+            if (lazy) step = x_on_k1 ? x_next(c, seq - 1, seq >= 2 ? seq - 2 : 0) : x_next(c, seq >= 2 ? seq - 2 : 0, seq >= 3 ? seq - 3 : 0);
+            if ((rc = launch_bin(c, nullptr, n, bin_place(c, par), !x_on_k1 && step.world ? &step : nullptr)) != GT_OK) return rc;
+            if ((rc = launch_score(c, n, bin_place(c, par), false, x_on_k1 && step.world ? &step : nullptr)) != GT_OK) return rc;
             step_taken = true;
             if ((rc = launch_singular(c, nullptr, n, bin_place(c, par))) != GT_OK) return rc;
             c->scores_m = c->want_score_m;
@@ -632,9 +660,10 @@ int enqueue_scoring(gt_ctx *c, const uint32_t *d_ids, uint32_t n)
         }
         if ((rc = launch_argmin(c, bin_place(c, par))) != GT_OK) return rc;
     }
-    if (!step_taken && (rc = launch_exchange_step(c, step)) != GT_OK) return rc;
+    // paths without a step of their own: one-warp kernels behind the pass, reduce(seq-2) and post(seq-1)
+    if (lazy && !step_taken && (rc = x_catch_up(c, seq - 1, seq >= 2 ? seq - 2 : 0)) != GT_OK) return rc;
     if (lazy) c->x_seq = seq;
-    else if ((rc = exchange_min(c, c->place_cur, par)) != GT_OK) return rc;
+    else if (!probe_no_x && (rc = exchange_min(c, c->place_cur, par)) != GT_OK) return rc;
     c->bin_parity ^= 1u;
     c->best_valid = true;
     c->place_valid = true;
@@ -2056,7 +2085,7 @@ extern "C" int gt_score_nodes_static(const uint8_t *d_cost, const uint8_t *d_n_g
     uint16_t *flist = reinterpret_cast<uint16_t *>(list + (size_t)gt::kBins * GT_STATIC_MAX_NODES);
     gt::k_bin<<<(n_nodes + gt::kCta - 1) / gt::kCta, gt::kCta, 0, s>>>(d_n_gpus, d_free_mask, nullptr, n_nodes,
                                                                      GT_STATIC_MAX_NODES, cnt, list, flist, d_best,
-                                                                     nullptr, nullptr, nullptr, 0u);
+                                                                     nullptr, nullptr, nullptr, 0u, gt::XWork{});
     gt::ScoreParams prm = {};
     prm.cost = d_cost; prm.best = d_best; prm.ctl = cnt; prm.bin_list = list; prm.bin_free = flist;
     prm.place = nullptr; prm.cap = GT_STATIC_MAX_NODES; prm.first_node = 0; prm.fold_place = 0; prm.keep_bins = 0; prm.zero = 0;

@@ -206,7 +206,8 @@ __device__ __forceinline__ void exchange_step(const XWork &w, uint32_t lane)
     reduce(w.seq_reduce2, w.out2);
     __syncwarp();
     if (w.keys_host) {       // the caller's copy, straight from here: the score write-back runs beside this kernel
-        if (lane < 16) w.keys_host[lane] = w.out2[lane];
+        const unsigned long long *last = w.seq_reduce2 ? w.out2 : w.out1;     // the step's last reduction
+        if (lane < 16) w.keys_host[lane] = last[lane];
         if (lane == 16) w.keys_host[16] = *reinterpret_cast<volatile unsigned long long *>(w.err_flag);
     }
 }
@@ -263,10 +264,23 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
                                               uint32_t *__restrict__ ctl, uint32_t *__restrict__ bin_list,
                                               uint16_t *__restrict__ bin_free, uint32_t *__restrict__ best,
                                               unsigned long long *__restrict__ place, uint8_t *__restrict__ scores,
-                                              uint16_t *__restrict__ free_copy, uint32_t early)
+                                              uint16_t *__restrict__ free_copy, uint32_t early, XWork xw)
 {
     __shared__ uint32_t s_cnt[kBins], s_base[kBins];
     const uint32_t tid = threadIdx.x;
+    // Multi-GPU: the grid has one CTA more than the nodes need, and that one (CTA 0, the first to become resident)
+    // carries a step of the key exchange in one warp -- before the dependency wait when K0 runs ahead, i.e. beside the
+    // last units of the previous pass's K1.  What it posts are the keys of the pass before that one (complete: the K1
+    // in front waited for its K0, which waited for that pass's K1).
+    const uint32_t has_x = xw.world != 0 ? 1u : 0u;
+    if (has_x && blockIdx.x == 0) {
+        if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
+        if (tid < 32) exchange_step(xw, tid);
+        if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;");
+        return;
+    }
+    const uint32_t blk = blockIdx.x - has_x;
 #ifdef GT_TRACE
     if (tid == 0) GT_KT_MIN(0, gt_now());
 #endif
@@ -285,7 +299,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     // ones when the mirror is read in place -- was measured: 0.3 us slower per resident pass for the extra barrier,
     // no gain end to end: profiles/r2_k0_wide_loads_ab.txt)
     __syncthreads();
-    const uint32_t i = blockIdx.x * blockDim.x + tid;
+    const uint32_t i = blk * blockDim.x + tid;
     int p = -1;
     uint32_t slot = 0, node = 0, f = 0, raw = 0;
     if (i < n) {
@@ -311,7 +325,7 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
     }
     if (early == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
     // what the previous pass's kernels may still have been reading or writing
-    if (place && blockIdx.x == 0 && tid < 16) place[tid] = ~0ull;
+    if (place && blk == 0 && tid < 16) place[tid] = ~0ull;
     if (p >= 0) {
         // free_mask may be the caller's pinned host mirror read in place (whole-shard update): the device copy that
         // later passes over single nodes read is refreshed on the way, no separate upload
