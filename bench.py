@@ -522,7 +522,7 @@ def main():
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": workload_config(args, world, subsets[0]),
             "run": {"exchange": {0: "none (one rank)", 1: "16 placement keys, NCCL min all-reduce on a side stream",
-                                 2: "16 placement keys, own kernel over NVLink peer memory (k_exchange) on a side stream"}[ctxs[0].comm_mode()],
+                                 2: "16 placement keys over NVLink peer memory by one warp of the next pass's K1 (exchange_step), no kernel or stream of its own"}[ctxs[0].comm_mode()],
                     "l2": "%d cluster replicas rotated between steps (%.0f MB of tables > 126 MB L2)" % (R, read_mb)},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernels_us": kernels,
             "cpu_baseline": cpu_baseline, "placements": placements, "strong": strong, "checks": checks,
