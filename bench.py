@@ -65,7 +65,9 @@ class ClockSampler(threading.Thread):
         self.index, self.period, self.start_delay = index, period, start_delay
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._halt = threading.Event()
-        self.ok = False
+        self.active = threading.Event()    # samples count from here on (before: set-up, the GPU idles at low clocks)
+        self.quiet = threading.Event()     # set around timed regions of under ~5 ms: an NVML query can hold up kernel launches
+        self.ok = False                    # for 0.1-1 ms, which is most of such a region; the samples just before and after stand for it
         try:
             import pynvml
             self.nv = pynvml
@@ -89,12 +91,17 @@ class ClockSampler(threading.Thread):
         if self.start_delay:
             time.sleep(self.start_delay)
         while not self._halt.is_set():
+            if self.quiet.is_set():
+                time.sleep(0.0005)
+                continue
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
+                if self.active.is_set():
+                    self.samples.append(mhz)
+                    for bit, name in names.items():
+                        if r & bit:
+                            self.reasons.add(name)
             except Exception:
                 pass
             time.sleep(self.period)
@@ -106,7 +113,9 @@ class ClockSampler(threading.Thread):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
         return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+                "reasons": sorted(self.reasons), "samples": len(self.samples),
+                "sampling": "NVML every %d ms from the first warm-up pass to the end of the run, paused inside timed regions "
+                            "shorter than about 5 ms (a query can hold up kernel launches for most of such a region)" % int(self.period * 1e3)}
 
 
 def load_oracle():
@@ -237,25 +246,30 @@ def main():
         gt.score_all_async_many(cs, warmup)
         l0 = sum(r["ctx"].launch_count for r in reps)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if steps < 250:
+            sampler.quiet.set()
         barrier()
         e0.record(stream)
         gt.score_all_async_many(cs, steps)      # pass i on replica i % R; one call, so the host pays two launches per pass
         e1.record(stream)
         barrier()
+        sampler.quiet.clear()
         ms, total = over_ranks(e0.elapsed_time(e1), sum(reps[i % R]["subsets"] for i in range(steps)))
         return ms, total, sum(r["ctx"].launch_count for r in reps) - l0
 
     N = args.nodes_per_gpu
     R = max(1, args.replicas)
     first = rank * N
+    # started before the contexts are built: its first NVML calls (the slow ones) are over when the first clock starts
+    sampler = ClockSampler(local_rank, start_delay=float(os.environ.get("GT_BENCH_SAMPLER_DELAY", "0")))
+    if not os.environ.get("GT_BENCH_NO_SAMPLER"):
+        sampler.start()
     reps = make_contexts(4, SEED, first, N, R)
+    sampler.active.set()
     ctxs = [r["ctx"] for r in reps]
     subsets = [r["subsets"] for r in reps]
     read_mb = R * (N * 256 + N * 64) / 1e6
 
-    sampler = ClockSampler(local_rank, start_delay=float(os.environ.get("GT_BENCH_SAMPLER_DELAY", "0")))
-    if not os.environ.get("GT_BENCH_NO_SAMPLER"):
-        sampler.start()
 
     # ---- device-resident throughput (`value`): inputs already in HBM
     ms, total_subsets, launches = timed_passes(reps, args.steps, args.warmup)
@@ -319,14 +333,17 @@ def main():
     place_np = np.zeros(16, np.uint64)
 
     def run_cycles(cycle, steps):
-        for i in range(3):
+        for i in range(max(3, R)):       # untimed: every replica has answered one call of this kind before the clock starts
             cycle(i)
+        if steps < 100:
+            sampler.quiet.set()
         barrier()
         t0 = time.perf_counter()
         for i in range(steps):
             cycle(i)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        sampler.quiet.clear()
         return over_ranks(dt, sum(subsets[i % R] for i in range(steps)))
 
     # the informer's masks live in the context's own pinned mirror (gt_host_free) and the scores are read in place

@@ -135,6 +135,7 @@ struct gt_ctx {
     bool free_uploaded = true;    // device free[] equals the mirror except for `dirty`
     cudaEvent_t ev_h2d = nullptr; // last copy that reads the pinned mirrors (they may not change before it ran)
     bool h2d_pending = false;
+    bool mirror_read_in_flight = false;         // a K0 that reads the mirror in place has been queued and the stream not waited for since
     bool best_valid = false, place_valid = false;
     uint64_t launches = 0;
     void *comm = nullptr;
@@ -205,8 +206,17 @@ int mirror_writable(gt_ctx *c)
         GT_CUDA(c, cudaEventSynchronize(c->ev_h2d));
         c->h2d_pending = false;
     }
+    // a K0 reading the mirror in place leaves no event behind: one between K0 and K1 would make K1 an ordinary launch
+    // instead of a programmatic dependent.  Callers that wait for their passes (the `sort` cycle) never get here with
+    // the flag set (stream_waited_for); one that edits the mirror while a pass is in flight waits for that pass.
+    if (c->mirror_read_in_flight) {
+        GT_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->mirror_read_in_flight = false;
+    }
     return GT_OK;
 }
+
+void stream_waited_for(gt_ctx *c) { c->mirror_read_in_flight = false; }
 
 // bring the device free[] up to date with the host mirror
 int flush_free(gt_ctx *c, bool all)
@@ -312,9 +322,14 @@ int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long 
                                   (uint8_t *)((c->want_score_m && preset_place && !d_ids) ? c->d_scores : nullptr),
                                   (uint16_t *)(in_place ? c->d_free : nullptr), early, xwork));
     c->k0_inputs_pending = false;    // this K0, or its wait, is behind every write queued so far
-    if (in_place) {       // the mirror may not change before this K0 has read it
-        GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
-        c->h2d_pending = true;
+    if (in_place) {       // the mirror may not change before this K0 has read it (mirror_writable)
+        static const bool eager_event = getenv("GT_MIRROR_EVENT") != nullptr;     // A/B aid: the event of earlier builds
+        if (eager_event) {
+            GT_CUDA(c, cudaEventRecord(c->ev_h2d, c->stream));
+            c->h2d_pending = true;
+        } else {
+            c->mirror_read_in_flight = true;
+        }
         c->free_uploaded = true;
         c->masks_in_place = false;
     }
@@ -825,6 +840,7 @@ int gt_set_cost_lut(gt_ctx *c, const uint8_t lut[16])
     int rc = apply_lut(c, 0, c->n_nodes);
     if (rc != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     return GT_OK;
 }
 
@@ -923,6 +939,7 @@ int gt_gaia_select(gt_ctx *c, uint32_t m, uint32_t *out_best)
     GT_CUDA(c, cudaGetLastError());
     GT_CUDA(c, cudaMemcpyAsync(out_best, c->d_gaia_out, (size_t)c->n_nodes * 4, cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     return GT_OK;
 }
 
@@ -1027,6 +1044,7 @@ int gt_sync(gt_ctx *c)
     if (!c) return GT_ERR_INVALID;
     GT_CUDA(c, cudaSetDevice(c->device));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     return GT_OK;
 }
@@ -1038,6 +1056,7 @@ int gt_score_all(gt_ctx *c, uint32_t *out_best)
     if (out_best && c->n_nodes)
         GT_CUDA(c, cudaMemcpyAsync(out_best, c->d_best, (size_t)c->n_nodes * 64, cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     return GT_OK;
 }
 
@@ -1053,6 +1072,7 @@ int gt_score_dirty(gt_ctx *c)
     rc = enqueue_scoring(c, c->d_ids, n);
     if (rc != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     return GT_OK;
 }
 
@@ -1076,6 +1096,7 @@ int gt_best_node(gt_ctx *c, const uint8_t *k, uint32_t nreq, uint64_t *out_place
     if (c->comm && c->p2p)
         GT_CUDA(c, cudaMemcpyAsync(c->h_place + 16, c->d_xflags + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     if (c->comm && c->p2p && c->h_place[16] != 0) return exchange_failed(c);
     for (uint32_t i = 0; i < nreq; i++)
         out_place[i] = (k[i] >= 1 && k[i] <= 16) ? (uint64_t)c->h_place[k[i] - 1] : GT_NO_PLACE;
@@ -1091,6 +1112,7 @@ int gt_allocate(gt_ctx *c, uint32_t node, uint32_t k, uint16_t *out_mask, uint16
     GT_CUDA(c, cudaSetDevice(c->device));
     GT_CUDA(c, cudaMemcpyAsync(c->h_row, c->d_best + (size_t)node * 16, 64, cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     *out_mask = (uint16_t)GT_BEST_MASK(c->h_row[k - 1]);
     *out_cost = (uint16_t)GT_BEST_COST(c->h_row[k - 1]);
     return GT_OK;
@@ -1178,6 +1200,7 @@ int gt_time_kernel(gt_ctx *c, const char *which, uint32_t iters, float *out_ms)
     GT_CUDA(c, cudaMemsetAsync(cur_ctl(c), 0, gt::kCtlWords * sizeof(uint32_t), c->stream));
     if ((rc = enqueue_scoring(c, nullptr, c->n_nodes)) != GT_OK) return rc;
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     *out_ms = ms / (float)iters;
     return GT_OK;
 }
@@ -1251,6 +1274,7 @@ int gt_best_node_local(gt_ctx *c, uint64_t out_place[16])
     }
     GT_CUDA(c, cudaMemcpyAsync(c->h_place, scratch, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     memcpy(out_place, c->h_place, 16 * sizeof(uint64_t));
     return GT_OK;
 }
@@ -1377,6 +1401,7 @@ int gt_comm_init(gt_ctx *c, const uint8_t id[128], int rank, int world)
     for (auto &ev : c->ev_comm) GT_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     // one exchange now, so connections are set up before any timed or latency-critical pass
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     e = api->AllReduce(c->d_place, c->d_place, 16, kNcclUint64, kNcclMin, c->comm, c->comm_stream);
     if (e != 0) return fail(c, GT_ERR_NCCL, "ncclAllReduce (warm-up): %s", api->GetErrorString ? api->GetErrorString(e) : "?");
     GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
@@ -1551,6 +1576,7 @@ int schedule_sharded(gt_ctx *c, const uint8_t *ev_k, const uint32_t *ev_arg, uin
 {
     if (c->flags & GT_FLAG_NO_MEMO) return fail(c, GT_ERR_STATE, "gt_schedule: GT_FLAG_NO_MEMO is not available on a sharded context%s");
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     if (c->comm_stream) GT_CUDA(c, cudaStreamSynchronize(c->comm_stream));
     int rc;
     if ((rc = mirror_writable(c)) != GT_OK) return rc;
@@ -1812,6 +1838,7 @@ int gt_ext_sort(gt_ctx *c, uint32_t m, uint8_t *out_scores, uint64_t *out_place)
     GT_CUDA(c, cudaGetLastError());
     if (keys_by_step) GT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm[0], 0));   // later passes stay behind the exchange
     GT_CUDA(c, cudaStreamSynchronize(c->stream));
+    stream_waited_for(c);
     if (out_scores) memcpy(out_scores, c->h_scores, c->n_nodes);   // NULL: the caller reads gt_host_scores() in place
     if (out_place) {
         if (c->comm && c->p2p && c->h_place_map[16] != 0) return exchange_failed(c);

@@ -196,8 +196,9 @@ int gt_bind_annotations(uint16_t mask, int64_t assume_time, int assigned, char *
  * 16 placement keys (as gt_best_node for k = 1..16) fetched in the same synchronisation. */
 int gt_ext_sort(gt_ctx *ctx, uint32_t m, uint8_t *out_scores, uint64_t *out_place);
 /* The same cycle without host copies, for an extender that keeps the informer's view in pinned memory:
- * gt_host_free returns the context's own pinned mirror of the free masks (max_nodes u16; waits for an upload that
- * still reads it) -- write masks in place, then gt_host_free_changed(first, count) says which nodes changed (the whole
+ * gt_host_free returns the context's own pinned mirror of the free masks (max_nodes u16; waits for an upload, or a pass
+ * whose binning kernel reads the mirror in place, that is still in flight: call it again before every round of edits,
+ * do not keep the pointer across scoring calls that were not waited for) -- write masks in place, then gt_host_free_changed(first, count) says which nodes changed (the whole
  * shard: one bulk upload and a full pass by the next scoring call).  gt_ext_sort with out_scores == NULL leaves the
  * reply in the mapped pinned buffer gt_host_scores returns (n_nodes bytes, valid until the next gt_ext_sort). */
 uint16_t *gt_host_free(gt_ctx *ctx);
@@ -248,7 +249,11 @@ int gt_ext_bind_json(gt_ctx *ctx, const char *request, size_t len, int64_t assum
 int gt_ext_pod_deleted(gt_ctx *ctx, const char *pod_uid);
 
 /* ---- asynchronous / measurement surface ---- */
-int gt_score_all_async(gt_ctx *ctx);     /* enqueue scoring + cluster argmin, no copies, no sync */
+/* enqueue scoring + cluster argmin, no copies, no sync.  Passes enqueued back to back overlap at their seams: the
+ * binning kernel of a pass reads the masks and fills its bin lists while the scoring kernel of the pass before it is
+ * still finishing (separate lists and control blocks; results of a pass are complete before the next one touches the
+ * table).  Mask updates through the API are ordered with that automatically. */
+int gt_score_all_async(gt_ctx *ctx);
 /* `passes` scoring passes enqueued round-robin over n_ctx contexts (ctxs[i % n_ctx] for pass i), no copies, no sync:
  * a scoring loop whose per-pass host cost is the two kernel launches, not a call through the binding */
 int gt_score_all_async_many(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes);
