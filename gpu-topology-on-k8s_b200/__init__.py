@@ -33,7 +33,7 @@ EXPORTS = [
     "gt_set_node_names", "gt_ext_sort_json", "gt_ext_bind_json", "gt_ext_pod_deleted",
     "gt_level_from_p2plink", "gt_levels_from_p2plink", "gt_lut_cmax",
     "gt_time_pass_rotated", "gt_best_node_local", "gt_comm_share",
-    "gt_host_free", "gt_host_free_changed", "gt_host_scores", "gt_score_all_async_many",
+    "gt_host_free", "gt_host_free_changed", "gt_host_scores", "gt_score_all_async_many", "gt_score_all_async_many_timed",
 ]
 STATIC_MAX_NODES = 4096
 
@@ -174,6 +174,8 @@ def _lib():
         L.gt_host_scores.restype = C.POINTER(C.c_uint8)
     if hasattr(L, "gt_score_all_async_many"):
         L.gt_score_all_async_many.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32]
+    if hasattr(L, "gt_score_all_async_many_timed"):
+        L.gt_score_all_async_many_timed.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
     L.gt_comm_init.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int]
     L.gt_synth_cluster.argtypes = [C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, u8p, u8p, u16p, u8p, u8p, u16p]
     L.gt_schedule.argtypes = [C.c_void_p, u8p, u32p, C.c_uint32, u32p, u16p, u64p]
@@ -461,6 +463,15 @@ def score_all_async_many(allocators, passes):
     rc = _lib().gt_score_all_async_many(arr, len(allocators), passes)
     if rc:
         raise GtError(rc, "gt_score_all_async_many", "; ".join(_lib().gt_last_error(a._h).decode() for a in allocators[:1]))
+
+
+def score_all_async_many_timed(allocators, passes, ev_start=None, ev_stop=None):
+    """score_all_async_many between two CUDA events (raw cudaEvent_t handles, e.g. torch.cuda.Event.cuda_event of an event
+    that has been recorded once), recorded by the library directly around its launches."""
+    arr = (C.c_void_p * len(allocators))(*[a._h.value for a in allocators])
+    rc = _lib().gt_score_all_async_many_timed(arr, len(allocators), passes, C.c_void_p(ev_start or 0), C.c_void_p(ev_stop or 0))
+    if rc:
+        raise GtError(rc, "gt_score_all_async_many_timed", "; ".join(_lib().gt_last_error(a._h).decode() for a in allocators[:1]))
 
 
 def time_pass_rotated(allocators, iters=64):

@@ -1039,6 +1039,21 @@ int gt_score_all_async_many(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes)
     return GT_OK;
 }
 
+// the same loop between two CUDA events of the caller (cudaEvent_t, may be NULL), recorded on the first context's stream
+// right before the first launch and right after the last: a timed region without the caller's own call overhead
+// between the start event and the first kernel
+int gt_score_all_async_many_timed(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes, void *ev_start, void *ev_stop)
+{
+    if (!ctxs || !n_ctx || !ctxs[0]) return GT_ERR_INVALID;
+    gt_ctx *c0 = ctxs[0];
+    GT_CUDA(c0, cudaSetDevice(c0->device));
+    if (ev_start) GT_CUDA(c0, cudaEventRecord(static_cast<cudaEvent_t>(ev_start), c0->stream));
+    int rc = gt_score_all_async_many(ctxs, n_ctx, passes);
+    if (rc != GT_OK) return rc;
+    if (ev_stop) GT_CUDA(c0, cudaEventRecord(static_cast<cudaEvent_t>(ev_stop), c0->stream));
+    return GT_OK;
+}
+
 int gt_sync(gt_ctx *c)
 {
     if (!c) return GT_ERR_INVALID;

@@ -156,6 +156,17 @@ __device__ __forceinline__ bool wait_flag_bounded(const unsigned long long *flag
     }
 }
 
+// system-scope fence of the message-passing pattern below (flags written and read as volatile = relaxed.sys accesses):
+// acquire-release is all it needs; __threadfence_system() is the sequentially consistent one
+__device__ __forceinline__ void fence_sys()
+{
+#ifdef GT_X_FENCE_SC
+    __threadfence_system();
+#else
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+#endif
+}
+
 // The exchange, one warp, no kernel of its own in a loop of passes.  Every rank owns an inbox that all peers have
 // mapped (CUDA IPC): keys[world][2][16] then flags[world][2], slot parity = pass number & 1.
 //   post(s):   store this rank's 16 keys of pass s into slot [rank][s & 1] of every rank's inbox, fence, then raise
@@ -181,7 +192,7 @@ __device__ __forceinline__ void exchange_step(const XWork &w, uint32_t lane)
             if (lane == 0) *reinterpret_cast<volatile unsigned long long *>(w.err_flag) = seq;
             return;
         }
-        __threadfence_system();      // acquire: the keys are read after the flags were seen
+        fence_sys();      // acquire: the keys are read after the flags were seen
         if (lane < 16) {
             unsigned long long m = ~0ull;
             for (uint32_t r = 0; r < w.world; r++) {
@@ -199,7 +210,7 @@ __device__ __forceinline__ void exchange_step(const XWork &w, uint32_t lane)
             for (uint32_t q = 0; q < w.world; q++)
                 *reinterpret_cast<volatile unsigned long long *>(w.inbox[q] + (size_t)slot * 16 + lane) = key;
         }
-        __threadfence_system();      // release: keys before flags, on every peer
+        fence_sys();      // release: keys before flags, on every peer
         __syncwarp();
         if (lane < w.world) *reinterpret_cast<volatile unsigned long long *>(w.inbox[lane] + flags + slot) = w.seq_post;
     }

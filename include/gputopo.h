@@ -257,6 +257,9 @@ int gt_score_all_async(gt_ctx *ctx);
 /* `passes` scoring passes enqueued round-robin over n_ctx contexts (ctxs[i % n_ctx] for pass i), no copies, no sync:
  * a scoring loop whose per-pass host cost is the two kernel launches, not a call through the binding */
 int gt_score_all_async_many(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes);
+/* the same loop between two CUDA events of the caller (cudaEvent_t handles, either may be NULL), recorded on the first
+ * context's stream directly in front of the first launch and behind the last one */
+int gt_score_all_async_many_timed(gt_ctx **ctxs, uint32_t n_ctx, uint32_t passes, void *ev_start, void *ev_stop);
 int gt_sync(gt_ctx *ctx);
 void *gt_stream(gt_ctx *ctx);            /* the cudaStream_t work is enqueued on */
 const uint32_t *gt_device_best(gt_ctx *ctx);   /* device pointer of best[n_nodes][16] */

@@ -582,6 +582,12 @@ def test_scoring_loop_in_one_call_and_local_keys(gt, oracle):
         assert (keys == oracle.cluster_argmin(want)).all()
         assert (a.best_node_local() == keys).all()
         assert (a.score_all() == want).all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    e1.record(stream)
+    gt.score_all_async_many_timed(ctxs, 6, e0.cuda_event, e1.cuda_event)     # the library records the caller's events
+    torch.cuda.synchronize()
+    assert 0.005 < e0.elapsed_time(e1) < 50
     rest, k1, whole = gt.time_pass_rotated(ctxs, 12)
     assert 0 < k1 < whole < 1000 and rest > 0
     for a, want in zip(ctxs, wants):
