@@ -101,27 +101,39 @@ __device__ unsigned int g_kpass;
 #else
 #define GT_TR(id) do { } while (0)
 #endif
-// scratch control block (u32 words): [0..16] bin counts, [17] K1 unit ticket, [18] K1 finished CTAs.
-// All zero between scoring passes: K1's last CTA clears it.
+// scratch control block (u32 words): [0..16] bin counts, [17] K1 unit ticket, [18] K1 finished CTAs (self_clean launches).
+// Three of them take turns (api.cu, launch_score): the one a pass uses was zeroed by the K1 two passes earlier.
 constexpr int kCtlWords = 32;
 constexpr int kCtlTicket = 17, kCtlDone = 18;
 // K1 hands out work units bin by bin, costliest unit type first (measured per-unit times, profiles/): the
-// multi-node units of p = 9, 10 and the 32-node units of p = 8 are the long ones, tiny bins come last.
+// 32-node units of p = 7, 8 and the multi-node units of p = 9 .. 12 are the long ones, tiny bins come last.
 // Kept as immediates (5 bits per entry), not in constant memory: a cold constant-cache miss in front of every
 // warp's first unit costs more than the whole decode.
 __host__ __device__ constexpr int bin_order_host(int i)
 {
 #ifndef GT_BIN_ORDER
-#define GT_BIN_ORDER 0
+#define GT_BIN_ORDER 6
 #endif
-#ifndef GT_MIX_FROM
-#define GT_MIX_FROM 0
-#define GT_MIX_TO 0
-#endif
-#if GT_BIN_ORDER == 0
+    // A/B'd on the final hand-over structure, us per pass at 100 000 nodes (profiles/r2_bin_order_ab_v2.txt, _v3.txt):
+    // 0: 14.97  2: 14.81  3: 14.72  4: 14.67  5: 14.68  6: 14.62  7: 14.69  8: 14.75   (1 lost by 1.3-1.9 us earlier in the round)
+#if GT_BIN_ORDER == 0     // round 1
     constexpr int order[kBins] = {9, 10, 8, 13, 11, 12, 7, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
-#else                     // longest measured unit first
+#elif GT_BIN_ORDER == 1   // many-lanes-per-node units strictly before one-lane-per-node units
     constexpr int order[kBins] = {12, 11, 13, 16, 15, 14, 9, 10, 8, 7, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 2   // longest unit first by the per-unit times of profiles/r2_k_score_warp_timeline_cold_v2.txt
+    constexpr int order[kBins] = {7, 12, 8, 11, 16, 9, 13, 10, 14, 5, 6, 4, 15, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 3   // the round-1 order with the 128-subset one-lane-per-node units in front
+    constexpr int order[kBins] = {7, 9, 10, 8, 13, 11, 12, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 4
+    constexpr int order[kBins] = {7, 12, 8, 11, 9, 10, 13, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 5
+    constexpr int order[kBins] = {7, 8, 9, 10, 13, 11, 12, 16, 14, 15, 6, 5, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 6   // default: as 3, the split units by descending unit time, p = 5 before p = 6
+    constexpr int order[kBins] = {7, 9, 10, 8, 13, 11, 12, 16, 15, 14, 5, 6, 4, 3, 2, 1, 0};
+#elif GT_BIN_ORDER == 7
+    constexpr int order[kBins] = {7, 12, 9, 10, 8, 13, 11, 15, 14, 16, 6, 5, 4, 3, 2, 1, 0};
+#else
+    constexpr int order[kBins] = {7, 9, 10, 8, 13, 11, 12, 15, 14, 16, 6, 5, 4, 0, 1, 2, 3};
 #endif
     return order[i];
 }
