@@ -1,7 +1,7 @@
 export GT_NO_REBUILD=1
-GT_LIB=ab/filt.so timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1
+for v in cta320 cta640; do GT_LIB=ab/$v.so timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "synthetic or split or full_size or masks_change" 2>&1 | tail -1; done
 B="python bench.py --steps 2000 --warmup 50 --no-extras --no-cpu-baseline"
 for i in 1 2; do
-  for v in nofilt filt; do GT_LIB=ab/$v.so $B > gpurun_out/r2_filt_${v}_$i.json 2>/dev/null; done
+  for v in cta128 cta320 cta640; do GT_LIB=ab/$v.so $B > gpurun_out/r2_cta_${v}_$i.json 2>/dev/null; done
 done
-python tools/bench_brief.py gpurun_out/r2_filt_*.json | tee gpurun_out/r2_place_filter_v2_ab.txt
+python tools/bench_brief.py gpurun_out/r2_cta_*.json | tee gpurun_out/r2_score_cta_ab.txt
