@@ -28,7 +28,10 @@ constexpr int kMaxG = 16;
 constexpr int kBins = 17;            // popcount 0..16
 constexpr int kCta = 256;
 constexpr uint32_t kInf = 0xFFFF0000u;
-constexpr int kScoreCta = 128;       // K1: 4 independent warps per CTA
+#ifndef GT_SCORE_CTA
+#define GT_SCORE_CTA 128    // (32 / 64: no change; 320 / 640 through dynamic shared memory: slower, profiles/r2_score_cta_ab.txt)
+#endif
+constexpr int kScoreCta = GT_SCORE_CTA;   // K1: 4 independent warps per CTA
 #ifndef GT_K1_TRIGGER
 #define GT_K1_TRIGGER 2   // where K1 lets the next kernel's CTAs be scheduled: 0 = at exit, 1 = after its own wait, 2 = after its work loop
 #endif
