@@ -494,6 +494,9 @@ struct WarpBest {
 // One lane per node: the lowest (cost, node) of the warp's candidates for request sizes K0+1 .. K0+4 goes to
 // lanes K0 .. K0+3.  Straight-line on purpose: the four reductions of each stage are independent, so their
 // latencies overlap (a branchy per-k version measured ~250 ns per k).  Rows beyond p hold kInf and fold to a no-op.
+#ifndef GT_FOLD_SELECT
+#define GT_FOLD_SELECT 1
+#endif
 template <int K0>
 __device__ __forceinline__ void fold_small_warp4(WarpBest &wb, const uint32_t (&out)[16], uint32_t node, uint32_t lane)
 {
@@ -511,9 +514,20 @@ __device__ __forceinline__ void fold_small_warp4(WarpBest &wb, const uint32_t (&
         const uint32_t owner = __ffs(__ballot_sync(0xFFFFFFFFu, tie[q] && node == nmin[q])) - 1;
         bv[q] = __shfl_sync(0xFFFFFFFFu, out[K0 + q], (int)(owner & 31u));
     }
+#if GT_FOLD_SELECT
+    // lane K0 + q takes candidate q: pick the lane's candidate first, compare once (four predicated compare chains
+    // were 5 % of K1's instructions)
+    const uint32_t q = lane - (uint32_t)K0;
+    uint32_t v = bv[0], n = nmin[0], cm = cmin[0];
+#pragma unroll
+    for (int j = 1; j < 4; j++)
+        if (q == (uint32_t)j) { v = bv[j]; n = nmin[j]; cm = cmin[j]; }
+    if (q < 4u && cm != kInf) wb.take(v, n);
+#else
 #pragma unroll
     for (int q = 0; q < 4; q++)
         if (lane == (uint32_t)(K0 + q) && cmin[q] != kInf) wb.take(bv[q], nmin[q]);
+#endif
 }
 
 // ---------------------------------------------------------------- K1 big: p > 8, 2^(p-8) lanes per node
