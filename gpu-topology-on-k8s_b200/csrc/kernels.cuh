@@ -660,9 +660,13 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     copies_landed();
     __syncwarp();
     GT_TR(11);   // tiles staged
+#ifndef GT_BIG_TICKET_BEFORE_TREE
+#define GT_BIG_TICKET_BEFORE_TREE 0   // 1 was measured: 1 us per pass slower (a unit reserved for 3 us while other warps run dry)
+#endif
+    if (GT_LATE_TICKET && GT_BIG_TICKET_BEFORE_TREE) next = take_ticket(prm, lane);
     if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
     __syncwarp();
-    if (GT_LATE_TICKET) next = take_ticket(prm, lane);   // (lane 0 only, see there) the reply arrives during the write-out
+    if (GT_LATE_TICKET && !GT_BIG_TICKET_BEFORE_TREE) next = take_ticket(prm, lane);   // (lane 0 only, see there) the reply arrives during the write-out
     GT_TR(12);   // set-up + tree + atomics done
     if (hb <= 5) {
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
@@ -845,6 +849,12 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 copies_landed();
                 __syncwarp();
             }
+#ifndef GT_SMALL_TICKET_AT
+#define GT_SMALL_TICKET_AT 9    // one-lane-per-node units of bins below this p ask for the next unit in front of their tree, once
+#endif                          // the tiles are staged (us per pass: 0: 14.54, 5: 14.55, 7: 14.40, 8: 14.42, 9: 14.32;
+                                // many-lanes-per-node units the same way: 15.36; everybody at the start of the unit: 15.9;
+                                // profiles/r2_small_ticket_ab*.txt, r2_ticket_timing_ab_v3.txt)
+            if (GT_LATE_TICKET && p < GT_SMALL_TICKET_AT) next = take_ticket(prm, lane);
             if (ok) {
                 score_small_any<true>(p, ws.raw + lane * kTileStride, f, out);
 #else
@@ -859,7 +869,11 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
                 o[3] = make_uint4(kInf, kInf, kInf, kInf);
                 if (prm.score_k) prm.scores[node] = (uint8_t)score_byte(pick_row(out, prm.score_k), prm.score_den);
             }
-            if (GT_LATE_TICKET) next = take_ticket(prm, lane);   // (lane 0 only) the reply arrives during the fold
+#if GT_SMALL_SMEM
+            if (GT_LATE_TICKET && p >= GT_SMALL_TICKET_AT) next = take_ticket(prm, lane);   // (lane 0 only) the reply arrives during the fold
+#else
+            if (GT_LATE_TICKET) next = take_ticket(prm, lane);
+#endif
             if (prm.fold_place) {
                 fold_small_warp4<0>(wb, out, node, lane);
                 if (p > 4) fold_small_warp4<4>(wb, out, node, lane);

@@ -1,7 +1,6 @@
 export GT_NO_REBUILD=1
-GT_LIB=ab/fold1.so timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1
 B="python bench.py --steps 2000 --warmup 50 --no-extras --no-cpu-baseline"
-for i in 1 2 3; do
-  for v in fold0 fold1; do GT_LIB=ab/$v.so $B > gpurun_out/r2_fold_${v}_$i.json 2>/dev/null; done
+for i in 1 2; do
+  for v in tk9 bigtree early_all; do GT_LIB=ab/$v.so $B > gpurun_out/r2_tkc_${v}_$i.json 2>/dev/null; done
 done
-python tools/bench_brief.py gpurun_out/r2_fold_*.json | tee gpurun_out/r2_fold_select_ab.txt
+python tools/bench_brief.py gpurun_out/r2_tkc_*.json | tee gpurun_out/r2_ticket_timing_ab_v3.txt
