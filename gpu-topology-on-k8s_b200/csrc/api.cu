@@ -290,7 +290,7 @@ gt::ScoreParams score_params(gt_ctx *c, unsigned long long *fold_into, bool keep
     return p;
 }
 
-// K0.  The control block is zero between passes (K1's last CTA clears it); preset_place: K1 will fold.
+// K0.  The control block it counts into is zero (three take turns, see launch_score); preset_place: K1 will fold.
 int launch_bin(gt_ctx *c, const uint32_t *d_ids, uint32_t n, unsigned long long *preset_place, const gt::XWork *xw = nullptr)
 {
     // programmatic dependent of the kernel in front of it (the previous pass's K1 in a scoring loop): the launch

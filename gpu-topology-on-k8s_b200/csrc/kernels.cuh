@@ -547,7 +547,11 @@ __device__ __forceinline__ uint32_t row_sum(const uint4 row, const uint32_t (&m)
 
 // one lane of a big node: subsets H (given by h over the free GPUs beyond the 8 lowest) x the 8-position tree.
 // raw: the node's 16x16 cost tile in shared memory, symmetric, zero diagonal, 16-byte aligned.
-__device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, int hb, uint32_t h, uint32_t *best_row)
+#ifndef GT_BIG_TICKET_MID
+#define GT_BIG_TICKET_MID 5     // the tree's top-level children b = 7 .. this are walked before `mid()` runs, the rest (2^b - 1 + 1
+#endif                          // subsets) after it: K1 asks for its next unit there, a few hundred nanoseconds before the tree ends
+template <class Mid>
+__device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, int hb, uint32_t h, uint32_t *best_row, Mid mid)
 {
     uint32_t pos[8], bit[8], c[64], R[8], acc[9];
 #pragma unroll
@@ -584,7 +588,17 @@ __device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, i
 #pragma unroll
     for (int k = 0; k <= 8; k++) acc[k] = kInf;
     if (h) acc[0] = key0;
+#if GT_BIG_TICKET_MID >= 8
     Children<8, 8, 0>::run(key0, R, c, bit, acc);
+    mid();
+#else
+    visit_child<8, 7, 0>(key0, R, c, bit, acc);
+    if (GT_BIG_TICKET_MID < 7) visit_child<8, 6, 0>(key0, R, c, bit, acc);
+    if (GT_BIG_TICKET_MID < 6) visit_child<8, 5, 0>(key0, R, c, bit, acc);
+    if (GT_BIG_TICKET_MID < 5) visit_child<8, 4, 0>(key0, R, c, bit, acc);
+    mid();
+    Children<8, (GT_BIG_TICKET_MID < 4 ? 4 : GT_BIG_TICKET_MID), 0>::run(key0, R, c, bit, acc);
+#endif
 #pragma unroll
     for (int j = 0; j <= 8; j++)
         if (acc[j] != kInf) atomicMin(best_row + nsel + j, acc[j]);
@@ -664,9 +678,13 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
 #define GT_BIG_TICKET_BEFORE_TREE 0   // 1 was measured: 1 us per pass slower (a unit reserved for 3 us while other warps run dry)
 #endif
     if (GT_LATE_TICKET && GT_BIG_TICKET_BEFORE_TREE) next = take_ticket(prm, lane);
-    if (active) score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0]);
+    // (the ticket instruction is a predicated one executed by whoever is here; lane 0 always is: slot 0 is live)
+    if (active)
+        score_big_lane(ws.raw + slot * kTileStride, f, hb, h, &ws.best[slot][0], [&]() {
+            if (GT_LATE_TICKET && !GT_BIG_TICKET_BEFORE_TREE && GT_BIG_TICKET_MID < 8) next = take_ticket(prm, lane);
+        });
     __syncwarp();
-    if (GT_LATE_TICKET && !GT_BIG_TICKET_BEFORE_TREE) next = take_ticket(prm, lane);   // (lane 0 only, see there) the reply arrives during the write-out
+    if (GT_LATE_TICKET && !GT_BIG_TICKET_BEFORE_TREE && GT_BIG_TICKET_MID >= 8) next = take_ticket(prm, lane);   // (lane 0 only, see there) the reply arrives during the write-out
     GT_TR(12);   // set-up + tree + atomics done
     if (hb <= 5) {
         // half-warps write one row per pass (k = (lane & 15) + 1) and keep the best candidate per k
@@ -695,8 +713,8 @@ __device__ __forceinline__ void score_big_warp(const ScoreParams &prm, WarpScrat
     __syncwarp();
 }
 
-// Persistent warps pull work units (heaviest bins first) from a global ticket, fetching the next ticket
-// before working on the current unit.
+// Persistent warps pull work units (costliest unit types first) from a global ticket; the ticket for the next unit is
+// asked for late in the current one (take_ticket, GT_SMALL_TICKET_AT), its reply is read at the end of the unit.
 //   bin p <= 8 : 32 nodes per unit (one lane each)
 //   bin 9..13  : 32 >> (p-8) nodes per unit
 //   bin >= 14  : 2^(p-13) units per node
@@ -755,10 +773,7 @@ __global__ void __launch_bounds__(kScoreCta, kScoreMinCtas) k_score(ScoreParams 
     const uint32_t total = __shfl_sync(0xFFFFFFFFu, my_end, kBins - 1);
     WarpScratch &ws = s_ws[warp];
     GT_TR(3);
-    // first unit = this warp's global index; later ones come from the ticket, requested one unit ahead.
-    // ptxas turns an atomic add on a provably warp-uniform address (even from inline PTX, even atom.inc) into
-    // a warp-aggregated atomic whose leader broadcast (SHFL) waits for the reply at once -- that stalled every
-    // warp in front of each unit.  The address therefore carries a run-time zero times the thread index.
+    // first unit = this warp's global index; later ones come from the ticket (take_ticket).
     // Multi-GPU: the last warp of CTA 0 carries the exchange step of the two passes before this one (see exchange_step).
     // It gets no unit of its own to start with -- the step costs it 2-3 us of NVLink round trips, and a unit waiting
     // behind that would end the kernel late -- and joins the others through the ticket afterwards.
@@ -1180,7 +1195,7 @@ __global__ void __launch_bounds__(pipe::kCta, pipe::kCtasPerSm) k_score_pipe(Sco
                 for (uint32_t s2 = 0; s2 < live; s2++)
                     if (lane < (uint32_t)kBins) my_best[s2][lane] = kInf;
                 __syncwarp();
-                if (active) score_big_lane(sl.raw + slot * kTileStride, sl.f[slot], hb, h, &my_best[slot][0]);
+                if (active) score_big_lane(sl.raw + slot * kTileStride, sl.f[slot], hb, h, &my_best[slot][0], []() {});
                 __syncwarp();
                 if (hb <= 5) {
                     WarpBest hb2;
