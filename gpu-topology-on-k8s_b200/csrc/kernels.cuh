@@ -548,8 +548,12 @@ __device__ __forceinline__ uint32_t row_sum(const uint4 row, const uint32_t (&m)
 // one lane of a big node: subsets H (given by h over the free GPUs beyond the 8 lowest) x the 8-position tree.
 // raw: the node's 16x16 cost tile in shared memory, symmetric, zero diagonal, 16-byte aligned.
 #ifndef GT_BIG_TICKET_MID
-#define GT_BIG_TICKET_MID 5     // the tree's top-level children b = 7 .. this are walked before `mid()` runs, the rest (2^b - 1 + 1
-#endif                          // subsets) after it: K1 asks for its next unit there, a few hundred nanoseconds before the tree ends
+#define GT_BIG_TICKET_MID 4     // the tree's top-level children b = 7 .. this are walked before `mid()` runs, the rest (2^b - 1
+#endif                          // subsets) after it: K1 asks for its next unit there, in front of the last 15 subsets and the
+                                // shared-memory minima, 0.5-0.8 us before the unit's tree phase ends.  us per pass: 8 (behind the
+                                // tree): 14.32, 6: 14.17, 5: 14.16, 4: 14.12, 3: 14.20, 2: 14.18, 1: 14.15 (profiles/
+                                // r2_big_ticket_mid_ab*.txt); the same inside the P = 7, 8 trees of one-lane-per-node units
+                                // instead of in front of them: +0.1 (r2_small_ticket_mid_ab_v2.txt)
 template <class Mid>
 __device__ __forceinline__ void score_big_lane(const uint8_t *raw, uint32_t f, int hb, uint32_t h, uint32_t *best_row, Mid mid)
 {
