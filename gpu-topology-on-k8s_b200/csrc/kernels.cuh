@@ -350,6 +350,12 @@ __global__ void __launch_bounds__(kCta) k_bin(const uint8_t *__restrict__ n_gpus
         bin_free[at] = (uint16_t)f;
     }
     if (early == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
+#ifndef GT_K0_TRIGGER_AFTER_WAIT
+#define GT_K0_TRIGGER_AFTER_WAIT 1
+#endif
+    // every CTA of this grid is resident and has done its share when it gets here: K1's CTAs may be scheduled while the
+    // presets below are written (they wait for this grid to complete before they read anything)
+    if (GT_K0_TRIGGER_AFTER_WAIT && early == 2) asm volatile("griddepcontrol.launch_dependents;");
     // what the previous pass's kernels may still have been reading or writing
     if (place && blk == 0 && tid < 16) place[tid] = ~0ull;
     if (p >= 0) {
