@@ -14,6 +14,7 @@ as written -- ONE 100 000-node cluster sharded over the N ranks.
 Prints ONE JSON line on rank 0.
 """
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -92,7 +93,7 @@ class ClockSampler(threading.Thread):
             time.sleep(self.start_delay)
         while not self._halt.is_set():
             if self.quiet.is_set():
-                time.sleep(0.0005)
+                time.sleep(0.005)          # (no busy polling: every wake-up of this thread takes the interpreter lock)
                 continue
             try:
                 mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
@@ -335,16 +336,19 @@ def main():
     place_np = np.zeros(16, np.uint64)
 
     def run_cycles(cycle, steps):
-        for i in range(max(3, R)):       # untimed: every replica has answered one call of this kind before the clock starts
-            cycle(i)
+        gc.collect()
+        gc.disable()                     # no collector pause inside the timed cycles (collected before the warm-up: it empties the caches)
         if steps < 100:
             sampler.quiet.set()
+        for i in range(max(3, R)):       # untimed: every replica has answered one call of this kind before the clock starts
+            cycle(i)
         barrier()
         t0 = time.perf_counter()
         for i in range(steps):
             cycle(i)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        gc.enable()
         sampler.quiet.clear()
         return over_ranks(dt, sum(subsets[i % R] for i in range(steps)))
 
